@@ -1,0 +1,1092 @@
+// Host side of the C ABI (include/memb_b200.h): file -> HBM loader, kernel
+// launchers, ReadersUnion fusion, pinned-memory helpers and the Builder glue.
+// The only compute outside this translation unit's kernels is the one-time host
+// parse; there is deliberately no CPU decode path in the product.
+#include "../../include/memb_b200.h"
+
+#include "builder.h"
+#include "fb_format.h"
+#include "kernels.cuh"
+#include "memb_file.h"
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <thread>
+#include <string>
+#include <vector>
+
+using namespace memb_b200;
+namespace K = memb_b200::kernels;
+
+namespace {
+
+thread_local std::string g_lastError;
+std::atomic<uint64_t> g_launches{0};
+std::atomic<int64_t> g_optLutReplicas{0};
+std::atomic<int64_t> g_optWarps{0};
+std::atomic<int64_t> g_optGeneric{0};
+
+struct StatusError {
+    memb_b200_status status;
+    std::string message;
+};
+
+[[noreturn]] void fail(memb_b200_status status, const std::string& message)
+{
+    throw StatusError{status, message};
+}
+
+void cudaCheck(cudaError_t err, const char* what)
+{
+    if (err != cudaSuccess) {
+        fail(MEMB_B200_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(err));
+    }
+}
+#define CUDA_CHECK(expr) cudaCheck((expr), #expr)
+
+// Runs `body`, mapping exceptions to status codes + last_error.
+template <class Fn>
+memb_b200_status guarded(Fn body)
+{
+    try {
+        body();
+        return MEMB_B200_OK;
+    } catch (const StatusError& e) {
+        g_lastError = e.message;
+        return e.status;
+    } catch (const fb::FormatError& e) {
+        g_lastError = e.what();
+        return MEMB_B200_ERR_FORMAT;
+    } catch (const std::bad_alloc&) {
+        g_lastError = "out of host memory";
+        return MEMB_B200_ERR_IO;
+    } catch (const std::exception& e) {
+        g_lastError = e.what();
+        return MEMB_B200_ERR_IO;
+    }
+}
+
+struct DeviceGuard {
+    int previous = -1;
+    explicit DeviceGuard(int device)
+    {
+        CUDA_CHECK(cudaGetDevice(&previous));
+        if (previous != device) {
+            CUDA_CHECK(cudaSetDevice(device));
+        } else {
+            previous = -1;
+        }
+    }
+    ~DeviceGuard()
+    {
+        if (previous >= 0) {
+            cudaSetDevice(previous);
+        }
+    }
+};
+
+double msSince(std::chrono::steady_clock::time_point t0)
+{
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+
+bool deviceIsBlackwell(int device)
+{
+    int major = 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device) != cudaSuccess) {
+        return false;
+    }
+    return major == 10;  // the fatbin holds sm_100a SASS only
+}
+
+// Growable device buffer.
+struct Scratch {
+    void* ptr = nullptr;
+    size_t bytes = 0;
+    void* ensure(size_t need)
+    {
+        if (need > bytes) {
+            if (ptr) {
+                CUDA_CHECK(cudaFree(ptr));
+                ptr = nullptr;
+                bytes = 0;
+            }
+            const size_t rounded = (need + (size_t(1) << 20) - 1) & ~((size_t(1) << 20) - 1);
+            CUDA_CHECK(cudaMalloc(&ptr, rounded));
+            bytes = rounded;
+        }
+        return ptr;
+    }
+    void release()
+    {
+        if (ptr) {
+            cudaFree(ptr);
+        }
+        ptr = nullptr;
+        bytes = 0;
+    }
+};
+
+template <class T>
+T* deviceUpload(const T* host, size_t count, uint64_t& accounted)
+{
+    T* d = nullptr;
+    const size_t bytes = std::max<size_t>(count * sizeof(T), 16);
+    CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&d), bytes));
+    if (count) {
+        CUDA_CHECK(cudaMemcpy(d, host, count * sizeof(T), cudaMemcpyHostToDevice));
+    }
+    accounted += bytes;
+    return d;
+}
+
+}  // namespace
+
+struct memb_b200_reader {
+    int device = 0;
+    int numSMs = 148;
+    size_t smemOptin = 0;
+    std::unique_ptr<MembFile> file;
+    memb_b200_load_stats stats{};
+    cudaStream_t stream = nullptr;
+    std::mutex mutex;  // serialises use of the scratch buffers
+
+    // vocabulary
+    char* dWords = nullptr;
+    uint32_t* dWordOffsets = nullptr;
+    unsigned long long* dSlots = nullptr;
+    uint32_t slotMask = 0;
+
+    // storage-specific
+    K::TrainedParams trained{};
+    uint32_t trainedWarps = 0;  // 0 => generic kernel
+    uint32_t trainedG = 4;
+    bool trainedEscape = false;
+    K::UniformParams uniform{};
+    K::FullParams full{};
+    std::vector<void*> owned;
+
+    Scratch scratchIds, scratchOut, scratchQuery, scratchOffsets;
+
+    ~memb_b200_reader()
+    {
+        for (void* p : owned) {
+            cudaFree(p);
+        }
+        if (dWords) cudaFree(dWords);
+        if (dWordOffsets) cudaFree(dWordOffsets);
+        if (dSlots) cudaFree(dSlots);
+        scratchIds.release();
+        scratchOut.release();
+        scratchQuery.release();
+        scratchOffsets.release();
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+
+namespace {
+
+// Direct-table LUT over the top `lutBits` bits of the window
+// (the GPU analogue of the table built in src/huffman_table_decoder.h:44-56;
+// fuzz in SURVEY §0 shows any table width decodes identically).
+std::vector<uint32_t> buildLut(const PrefixCodeTable& code, uint32_t lutBits)
+{
+    std::vector<uint32_t> lut(size_t(1) << lutBits, 0x8000u);
+    for (size_t i = 0; i < code.keys.size(); ++i) {
+        const uint32_t len = code.lengths[i];
+        const uint32_t entry = (static_cast<uint32_t>(code.keys[i]) << 18) | len;
+        if (len <= lutBits) {
+            const uint32_t first = static_cast<uint32_t>(code.codes[i]) << (lutBits - len);
+            const uint32_t count = 1u << (lutBits - len);
+            for (uint32_t k = 0; k < count; ++k) {
+                lut[first + k] = entry;
+            }
+        } else {
+            lut[code.codes[i] >> (len - lutBits)] = 0x8000u;  // escape: resolved bit-serially
+        }
+    }
+    return lut;
+}
+
+K::CanonicalCode buildCanonical(const PrefixCodeTable& code)
+{
+    K::CanonicalCode c;
+    std::memset(&c, 0, sizeof(c));
+    c.minLen = code.minLen;
+    c.maxLen = code.maxLen;
+    for (size_t i = 0; i < code.keys.size(); ++i) {
+        const uint32_t len = code.lengths[i];
+        if (c.count[len] == 0) {
+            c.firstCode[len] = code.codes[i];
+            c.firstIndex[len] = static_cast<uint16_t>(i);
+        }
+        c.count[len] += 1;
+        c.keys[i] = code.keys[i];
+    }
+    return c;
+}
+
+void buildVocabulary(memb_b200_reader& r)
+{
+    const MembFile& f = *r.file;
+    r.dWords = deviceUpload(f.words, f.wordsBytes, r.stats.device_bytes);
+    r.dWordOffsets = deviceUpload(f.wordOffsets.data(), f.wordOffsets.size(), r.stats.device_bytes);
+    uint64_t slots = 16;
+    while (slots < 2 * f.rows) {
+        slots <<= 1;
+    }
+    r.slotMask = static_cast<uint32_t>(slots - 1);
+    CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&r.dSlots), slots * 8));
+    r.stats.device_bytes += slots * 8;
+    CUDA_CHECK(cudaMemsetAsync(r.dSlots, 0xff, slots * 8, r.stream));
+    if (f.rows) {
+        const uint32_t rows = static_cast<uint32_t>(f.rows);
+        K::hash_build_kernel<<<(rows + 255) / 256, 256, 0, r.stream>>>(r.dWords, r.dWordOffsets, rows, r.dSlots,
+                                                                     r.slotMask);
+        ++g_launches;
+        CUDA_CHECK(cudaGetLastError());
+    }
+}
+
+void loadTrained(memb_b200_reader& r)
+{
+    MembFile& f = *r.file;
+    const uint32_t rows = static_cast<uint32_t>(f.rows);
+    const auto t0 = std::chrono::steady_clock::now();
+
+    uint64_t tempBytes = 0;
+    uint8_t* dPacked = deviceUpload(f.packedValues, f.packedSize, tempBytes);
+    uint32_t* dValueOffsets = deviceUpload(f.valueOffsets.data(), f.valueOffsets.size(), tempBytes);
+    const K::CanonicalCode canonical = buildCanonical(f.code);
+    K::CanonicalCode* dCode = deviceUpload(&canonical, 1, r.stats.device_bytes);
+    r.owned.push_back(dCode);
+    float* dCodebook = deviceUpload(f.centroids.data(), f.centroids.size(), r.stats.device_bytes);
+    r.owned.push_back(dCodebook);
+    r.stats.upload_ms += msSince(t0);
+
+    const auto t1 = std::chrono::steady_clock::now();
+    // exact row lengths -> offsets of the 16 B-aligned re-pack
+    uint32_t* dRowBytes = nullptr;
+    CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&dRowBytes), std::max<size_t>(size_t(rows) * 4, 16)));
+    if (rows) {
+        K::measure_rows_kernel<<<(rows + 127) / 128, 128, 0, r.stream>>>(dPacked, f.packedSize, dValueOffsets, rows,
+                                                                       f.dim, dCode, dRowBytes);
+        ++g_launches;
+        CUDA_CHECK(cudaGetLastError());
+    }
+    std::vector<uint32_t> rowBytes(rows);
+    CUDA_CHECK(cudaMemcpyAsync(rowBytes.data(), dRowBytes, size_t(rows) * 4, cudaMemcpyDeviceToHost, r.stream));
+    CUDA_CHECK(cudaStreamSynchronize(r.stream));
+    std::vector<uint32_t> rowOff16(size_t(rows) + 1);
+    uint64_t units = 0, payload = 0;
+    uint32_t maxRowBytes = 0;
+    for (uint32_t i = 0; i < rows; ++i) {
+        rowOff16[i] = static_cast<uint32_t>(units);
+        units += (rowBytes[i] + 15) / 16;
+        payload += rowBytes[i];
+        maxRowBytes = std::max(maxRowBytes, rowBytes[i]);
+        if (units > 0xffffffffULL) {
+            fail(MEMB_B200_ERR_FORMAT, "memb file: re-packed rows exceed 64 GiB");
+        }
+    }
+    rowOff16[rows] = static_cast<uint32_t>(units);
+    r.stats.payload_bytes = payload;
+    uint32_t* dRowOff16 = deviceUpload(rowOff16.data(), rowOff16.size(), r.stats.device_bytes);
+    r.owned.push_back(dRowOff16);
+    uint4* dBlob = nullptr;
+    // one spare unit so the decoder's 96-bit window never leaves the allocation
+    const size_t blobBytes = (units + 1) * 16;
+    CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&dBlob), blobBytes));
+    r.stats.device_bytes += blobBytes;
+    r.owned.push_back(dBlob);
+    CUDA_CHECK(cudaMemsetAsync(reinterpret_cast<unsigned char*>(dBlob) + units * 16, 0, 16, r.stream));
+    if (rows) {
+        const uint64_t threads = uint64_t(rows) * 32;
+        K::repack_rows_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, r.stream>>>(
+            dPacked, f.packedSize, dValueOffsets, dRowBytes, dRowOff16, rows, reinterpret_cast<uint32_t*>(dBlob));
+        ++g_launches;
+        CUDA_CHECK(cudaGetLastError());
+    }
+
+    // decode tables
+    const uint32_t maxLen = f.code.maxLen;
+    int64_t replicasOpt = g_optLutReplicas.load();
+    uint32_t replicas, lutBits;
+    if (replicasOpt == 32 || (replicasOpt == 0 && maxLen <= 9)) {
+        replicas = 32;
+        lutBits = std::max(1u, std::min(maxLen, 9u));
+    } else {
+        replicas = 1;
+        lutBits = std::max(1u, std::min(maxLen, 12u));
+    }
+    const std::vector<uint32_t> lut = buildLut(f.code, lutBits);
+    uint32_t* dLut = deviceUpload(lut.data(), lut.size(), r.stats.device_bytes);
+    r.owned.push_back(dLut);
+
+    K::TrainedParams& p = r.trained;
+    p.blob = dBlob;
+    p.rowOff16 = dRowOff16;
+    p.lut = dLut;
+    p.codebook = dCodebook;
+    p.code = dCode;
+    p.rows = rows;
+    p.dim = f.dim;
+    p.lutBits = lutBits;
+    p.lutReplicas = replicas;
+    p.lutShift = (replicas == 32 ? 25 : 30) - lutBits;
+    p.lutMask = ((1u << lutBits) - 1) << (replicas == 32 ? 7 : 2);
+    p.codebookSize = static_cast<uint32_t>(f.centroids.size());
+    p.slotBytes = ((maxRowBytes + 15) / 16) * 16 + 16;
+    r.trainedEscape = maxLen > lutBits;
+    r.trainedG = maxLen <= 8 ? 8 : 4;
+
+    const size_t fixedBytes = K::trainedLutBytes(lutBits, replicas) + K::trainedCodebookBytes(p.codebookSize);
+    const size_t perWarp = K::trainedWarpBytes(p.slotBytes);
+    uint32_t warps = 0;
+    if (r.smemOptin > fixedBytes) {
+        warps = static_cast<uint32_t>(std::min<size_t>(K::TRAINED_MAX_WARPS, (r.smemOptin - fixedBytes) / perWarp));
+    }
+    const int64_t warpsOpt = g_optWarps.load();
+    if (warpsOpt > 0) {
+        warps = std::min<uint32_t>(warps, static_cast<uint32_t>(warpsOpt));
+    }
+    if (f.dim > K::TRAINED_MAX_DIM || g_optGeneric.load()) {
+        warps = 0;
+    }
+    r.trainedWarps = warps;
+
+    r.stats.max_code_len = maxLen;
+    r.stats.lut_bits = lutBits;
+    r.stats.lut_replicas = replicas;
+    r.stats.codebook_size = p.codebookSize;
+
+    CUDA_CHECK(cudaStreamSynchronize(r.stream));
+    CUDA_CHECK(cudaFree(dPacked));
+    CUDA_CHECK(cudaFree(dValueOffsets));
+    CUDA_CHECK(cudaFree(dRowBytes));
+    r.stats.prepare_ms += msSince(t1);
+    std::vector<uint32_t>().swap(f.valueOffsets);
+}
+
+void loadUniform(memb_b200_reader& r)
+{
+    MembFile& f = *r.file;
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<float2> minmax(f.rows);
+    for (uint64_t i = 0; i < f.rows; ++i) {
+        minmax[i] = make_float2(f.uniformMin[i], f.uniformMax[i]);
+        r.stats.payload_bytes += f.dim + 8;
+    }
+    uint8_t* dValues = deviceUpload(f.uniformValues.data(), f.uniformValues.size(), r.stats.device_bytes);
+    float2* dMinMax = deviceUpload(minmax.data(), minmax.size(), r.stats.device_bytes);
+    r.owned.push_back(dValues);
+    r.owned.push_back(dMinMax);
+    r.uniform.values = dValues;
+    r.uniform.minmax = dMinMax;
+    r.uniform.rows = static_cast<uint32_t>(f.rows);
+    r.uniform.dim = f.dim;
+    // quantization_levels is a uint8 promoted to float in the reference's
+    // `... * floatValue / quantizationLevels` (src/uniform_compression.cpp:68-72)
+    r.uniform.levels = static_cast<float>(f.quantizationLevels);
+    r.stats.upload_ms += msSince(t0);
+    std::vector<uint8_t>().swap(f.uniformValues);
+    std::vector<float>().swap(f.uniformMin);
+    std::vector<float>().swap(f.uniformMax);
+}
+
+void loadFull(memb_b200_reader& r)
+{
+    MembFile& f = *r.file;
+    const auto t0 = std::chrono::steady_clock::now();
+    float* dValues = deviceUpload(f.fullValues.data(), f.fullValues.size(), r.stats.device_bytes);
+    r.owned.push_back(dValues);
+    r.full.values = dValues;
+    r.full.rows = static_cast<uint32_t>(f.rows);
+    r.full.dim = f.dim;
+    r.stats.payload_bytes = uint64_t(f.rows) * f.dim * 4;
+    r.stats.upload_ms += msSince(t0);
+    std::vector<float>().swap(f.fullValues);
+}
+
+}  // namespace
+
+// ------------------------------------------------------------- launchers ----
+namespace {
+
+bool vec4Ok(uint32_t dim, const K::OutputSpec& o)
+{
+    return dim % 4 == 0 && o.rowStride % 4 == 0 && o.colOffset % 4 == 0 &&
+           reinterpret_cast<uintptr_t>(o.out) % 16 == 0;
+}
+
+template <int G, bool VEC4, bool ESCAPE>
+void launchTrainedEpi(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
+                      const K::OutputSpec& o, int epi, cudaStream_t stream)
+{
+    const K::TrainedParams& p = r.trained;
+    const size_t smemBytes = K::trainedLutBytes(p.lutBits, p.lutReplicas) + K::trainedCodebookBytes(p.codebookSize) +
+                             size_t(r.trainedWarps) * K::trainedWarpBytes(p.slotBytes);
+    const uint64_t tiles = (n + 31) / 32;
+    const unsigned grid = static_cast<unsigned>(
+        std::min<uint64_t>(static_cast<uint64_t>(r.numSMs), (tiles + r.trainedWarps - 1) / r.trainedWarps));
+    const unsigned block = r.trainedWarps * 32;
+    auto launch = [&](auto kernel) {
+        CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemBytes)));
+        kernel<<<grid, block, smemBytes, stream>>>(p, ids, rowBegin, n, o);
+    };
+    switch (epi) {
+    case K::EPI_WRITE:
+        launch(K::trained_decode_kernel<G, VEC4, ESCAPE, K::EPI_WRITE>);
+        break;
+    case K::EPI_ACCUMULATE:
+        launch(K::trained_decode_kernel<G, VEC4, ESCAPE, K::EPI_ACCUMULATE>);
+        break;
+    default:
+        launch(K::trained_decode_kernel<G, VEC4, ESCAPE, K::EPI_FINALIZE>);
+        break;
+    }
+}
+
+template <int G, bool VEC4>
+void launchTrainedEsc(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
+                      const K::OutputSpec& o, int epi, cudaStream_t stream)
+{
+    if (r.trainedEscape) {
+        launchTrainedEpi<G, VEC4, true>(r, ids, rowBegin, n, o, epi, stream);
+    } else {
+        launchTrainedEpi<G, VEC4, false>(r, ids, rowBegin, n, o, epi, stream);
+    }
+}
+
+// Decodes n rows (ids, or the range starting at rowBegin when ids == nullptr)
+// of one reader into `o` with the given epilogue.
+void launchDecode(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
+                  const K::OutputSpec& o, int epi, cudaStream_t stream)
+{
+    if (n == 0) {
+        return;
+    }
+    const uint32_t dim = r.file->dim;
+    const bool vec = vec4Ok(dim, o);
+    const uint64_t elems = n * (vec ? dim / 4 : dim);
+    const unsigned flatGrid = static_cast<unsigned>(std::min<uint64_t>((elems + 255) / 256, uint64_t(r.numSMs) * 32));
+    switch (r.file->storage) {
+    case STORAGE_TRAINED:
+        if (r.trainedWarps == 0) {
+            const unsigned grid = static_cast<unsigned>((n + 127) / 128);
+            if (epi == K::EPI_WRITE) {
+                K::trained_decode_generic_kernel<K::EPI_WRITE><<<grid, 128, 0, stream>>>(r.trained, ids, rowBegin, n, o);
+            } else if (epi == K::EPI_ACCUMULATE) {
+                K::trained_decode_generic_kernel<K::EPI_ACCUMULATE><<<grid, 128, 0, stream>>>(r.trained, ids, rowBegin, n, o);
+            } else {
+                K::trained_decode_generic_kernel<K::EPI_FINALIZE><<<grid, 128, 0, stream>>>(r.trained, ids, rowBegin, n, o);
+            }
+        } else if (r.trainedG == 8) {
+            vec ? launchTrainedEsc<8, true>(r, ids, rowBegin, n, o, epi, stream)
+                : launchTrainedEsc<8, false>(r, ids, rowBegin, n, o, epi, stream);
+        } else {
+            vec ? launchTrainedEsc<4, true>(r, ids, rowBegin, n, o, epi, stream)
+                : launchTrainedEsc<4, false>(r, ids, rowBegin, n, o, epi, stream);
+        }
+        break;
+    case STORAGE_UNIFORM: {
+        auto go = [&](auto kernel) { kernel<<<flatGrid, 256, 0, stream>>>(r.uniform, ids, rowBegin, n, o); };
+        if (vec) {
+            epi == K::EPI_WRITE        ? go(K::uniform_decode_kernel<true, K::EPI_WRITE>)
+            : epi == K::EPI_ACCUMULATE ? go(K::uniform_decode_kernel<true, K::EPI_ACCUMULATE>)
+                                       : go(K::uniform_decode_kernel<true, K::EPI_FINALIZE>);
+        } else {
+            epi == K::EPI_WRITE        ? go(K::uniform_decode_kernel<false, K::EPI_WRITE>)
+            : epi == K::EPI_ACCUMULATE ? go(K::uniform_decode_kernel<false, K::EPI_ACCUMULATE>)
+                                       : go(K::uniform_decode_kernel<false, K::EPI_FINALIZE>);
+        }
+        break;
+    }
+    default: {
+        auto go = [&](auto kernel) { kernel<<<flatGrid, 256, 0, stream>>>(r.full, ids, rowBegin, n, o); };
+        if (vec) {
+            epi == K::EPI_WRITE        ? go(K::full_gather_kernel<true, K::EPI_WRITE>)
+            : epi == K::EPI_ACCUMULATE ? go(K::full_gather_kernel<true, K::EPI_ACCUMULATE>)
+                                       : go(K::full_gather_kernel<true, K::EPI_FINALIZE>);
+        } else {
+            epi == K::EPI_WRITE        ? go(K::full_gather_kernel<false, K::EPI_WRITE>)
+            : epi == K::EPI_ACCUMULATE ? go(K::full_gather_kernel<false, K::EPI_ACCUMULATE>)
+                                       : go(K::full_gather_kernel<false, K::EPI_FINALIZE>);
+        }
+        break;
+    }
+    }
+    ++g_launches;
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void launchResolve(const memb_b200_reader& r, const char* dQuery, const uint64_t* dOffsets, uint64_t n,
+                   int32_t* dIds, cudaStream_t stream)
+{
+    if (n == 0) {
+        return;
+    }
+    K::resolve_words_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(
+        dQuery, dOffsets, n, r.dWords, r.dWordOffsets, r.dSlots, r.slotMask, dIds);
+    ++g_launches;
+    CUDA_CHECK(cudaGetLastError());
+}
+
+// Upper bound of rows decoded per pass when the result has to travel to the
+// host through the scratch buffer (4 GiB of fp32).
+uint64_t rowsPerPass(uint64_t rowFloats)
+{
+    const uint64_t cap = (uint64_t(4) << 30) / (std::max<uint64_t>(rowFloats, 1) * 4);
+    return std::max<uint64_t>(cap, 32);
+}
+
+// The ReadersUnion merge as a sequence of fused epilogues
+// (python/memb/readers_union.py:16-18,30-32):
+//   concatenate: reader r WRITEs its columns [sum dim_<r, sum dim_<=r)
+//   average:     reader 0 WRITEs, readers 1..R-2 ACCUMULATE, reader R-1 FINALIZEs
+// There is never a per-reader temporary.  ids: R*n reader-major (device).
+void launchUnion(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_mode mode, const int32_t* dIds,
+                 uint64_t idStride, uint64_t first, uint64_t n, float* dOut, uint64_t unionDim, cudaStream_t stream)
+{
+    uint32_t col = 0;
+    for (uint32_t k = 0; k < R; ++k) {
+        K::OutputSpec o;
+        o.out = dOut;
+        o.rowStride = unionDim;
+        o.divisor = static_cast<float>(R);
+        int epi = K::EPI_WRITE;
+        if (mode == MEMB_B200_CONCATENATE) {
+            o.colOffset = col;
+            col += readers[k]->file->dim;
+        } else {
+            o.colOffset = 0;
+            epi = k == 0 ? K::EPI_WRITE : (k + 1 == R ? K::EPI_FINALIZE : K::EPI_ACCUMULATE);
+        }
+        launchDecode(*readers[k], dIds + k * idStride + first, 0, n, o, epi, stream);
+    }
+}
+
+uint64_t unionDimOf(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_mode mode)
+{
+    if (R < 2) {
+        // python/memb/readers_union.py:59-60
+        fail(MEMB_B200_ERR_ARGUMENT, "You must pass at least 2 readers to create a union");
+    }
+    uint64_t total = 0;
+    for (uint32_t k = 0; k < R; ++k) {
+        if (!readers[k]) {
+            fail(MEMB_B200_ERR_ARGUMENT, "null reader in union");
+        }
+        if (readers[k]->device != readers[0]->device) {
+            fail(MEMB_B200_ERR_ARGUMENT, "all readers of a union must live on the same device");
+        }
+        if (mode == MEMB_B200_AVERAGE && readers[k]->file->dim != readers[0]->file->dim) {
+            // python/memb/readers_union.py:7-10
+            fail(MEMB_B200_ERR_ARGUMENT, "Dimensions of all readers must be equal for average mode");
+        }
+        total += readers[k]->file->dim;
+    }
+    return mode == MEMB_B200_AVERAGE ? readers[0]->file->dim : total;
+}
+
+}  // namespace
+
+// ----------------------------------------------------------------- C ABI ----
+extern "C" {
+
+const char* memb_b200_last_error(void)
+{
+    return g_lastError.c_str();
+}
+
+int memb_b200_device_count(void)
+{
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    int usable = 0;
+    for (int d = 0; d < count; ++d) {
+        usable += deviceIsBlackwell(d) ? 1 : 0;
+    }
+    return usable;
+}
+
+uint64_t memb_b200_launch_count(void)
+{
+    return g_launches.load();
+}
+
+memb_b200_status memb_b200_set_option(const char* name, int64_t value)
+{
+    return guarded([&] {
+        const std::string key = name ? name : "";
+        if (key == "trained_lut_replicas" && (value == 0 || value == 1 || value == 32)) {
+            g_optLutReplicas = value;
+        } else if (key == "trained_warps" && value >= 0 && value <= K::TRAINED_MAX_WARPS) {
+            g_optWarps = value;
+        } else if (key == "trained_generic" && (value == 0 || value == 1)) {
+            g_optGeneric = value;
+        } else {
+            fail(MEMB_B200_ERR_ARGUMENT, "unknown option or value out of range: " + key);
+        }
+    });
+}
+
+memb_b200_status memb_b200_open(const char* path, int device, unsigned num_threads, memb_b200_reader** out)
+{
+    return guarded([&] {
+        if (!path || !out) {
+            fail(MEMB_B200_ERR_ARGUMENT, "open: null argument");
+        }
+        *out = nullptr;
+        auto reader = std::make_unique<memb_b200_reader>();
+        const auto t0 = std::chrono::steady_clock::now();
+        const unsigned threads = num_threads ? num_threads : std::max(std::thread::hardware_concurrency(), 2u);
+        try {
+            reader->file = parseMembFile(path, threads);
+        } catch (const fb::FormatError&) {
+            throw;
+        } catch (const std::runtime_error& e) {
+            const std::string what = e.what();
+            if (what == "File format verification failed") {
+                fail(MEMB_B200_ERR_FORMAT, what);
+            }
+            if (what.rfind("Storage strategy", 0) == 0) {
+                fail(MEMB_B200_ERR_UNSUPPORTED, what);
+            }
+            fail(MEMB_B200_ERR_IO, what);
+        }
+        reader->stats.parse_ms = msSince(t0);
+
+        int count = 0;
+        if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+            cudaGetLastError();
+            fail(MEMB_B200_ERR_NO_DEVICE, "no CUDA device is visible; memb_b200 has no CPU path");
+        }
+        if (device < 0 || device >= count) {
+            fail(MEMB_B200_ERR_ARGUMENT, "device ordinal out of range");
+        }
+        if (!deviceIsBlackwell(device)) {
+            fail(MEMB_B200_ERR_NO_DEVICE, "device is not compute capability 10.x; kernels are built for sm_100a only");
+        }
+        reader->device = device;
+        DeviceGuard guard(device);
+        int value = 0;
+        CUDA_CHECK(cudaDeviceGetAttribute(&value, cudaDevAttrMultiProcessorCount, device));
+        reader->numSMs = value;
+        CUDA_CHECK(cudaDeviceGetAttribute(&value, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+        reader->smemOptin = static_cast<size_t>(value);
+        CUDA_CHECK(cudaStreamCreateWithFlags(&reader->stream, cudaStreamNonBlocking));
+
+        const auto t1 = std::chrono::steady_clock::now();
+        buildVocabulary(*reader);
+        reader->stats.upload_ms += msSince(t1);
+        switch (reader->file->storage) {
+        case STORAGE_TRAINED:
+            loadTrained(*reader);
+            break;
+        case STORAGE_UNIFORM:
+            loadUniform(*reader);
+            break;
+        default:
+            loadFull(*reader);
+            break;
+        }
+        const auto t2 = std::chrono::steady_clock::now();
+        CUDA_CHECK(cudaStreamSynchronize(reader->stream));
+        reader->stats.prepare_ms += msSince(t2);
+        // the mmap is only needed for the vocabulary text of trained files
+        if (reader->file->storage != STORAGE_TRAINED) {
+            reader->file->map.reset();
+        }
+        *out = reader.release();
+    });
+}
+
+void memb_b200_close(memb_b200_reader* reader)
+{
+    if (!reader) {
+        return;
+    }
+    int previous = -1;
+    cudaGetDevice(&previous);
+    cudaSetDevice(reader->device);
+    delete reader;
+    if (previous >= 0) {
+        cudaSetDevice(previous);
+    }
+}
+
+uint32_t memb_b200_dim(const memb_b200_reader* reader)
+{
+    return reader ? reader->file->dim : 0;
+}
+
+uint64_t memb_b200_rows(const memb_b200_reader* reader)
+{
+    return reader ? reader->file->rows : 0;
+}
+
+int memb_b200_storage_type(const memb_b200_reader* reader)
+{
+    return reader ? reader->file->storage : 0;
+}
+
+int memb_b200_device(const memb_b200_reader* reader)
+{
+    return reader ? reader->device : -1;
+}
+
+memb_b200_status memb_b200_get_load_stats(const memb_b200_reader* reader, memb_b200_load_stats* stats)
+{
+    return guarded([&] {
+        if (!reader || !stats) {
+            fail(MEMB_B200_ERR_ARGUMENT, "get_load_stats: null argument");
+        }
+        *stats = reader->stats;
+    });
+}
+
+memb_b200_status memb_b200_keys(const memb_b200_reader* reader, const char** words, const uint32_t** offsets,
+                                uint64_t* rows)
+{
+    return guarded([&] {
+        if (!reader || !words || !offsets || !rows) {
+            fail(MEMB_B200_ERR_ARGUMENT, "keys: null argument");
+        }
+        *words = reader->file->words;
+        *offsets = reader->file->wordOffsets.data();
+        *rows = reader->file->rows;
+    });
+}
+
+}  // extern "C"
+
+namespace {
+
+// Uploads the query text and resolves it to device ids in scratchIds.
+int32_t* resolveToDevice(memb_b200_reader& r, const char* queryBytes, const uint64_t* queryOffsets, uint64_t n,
+                         cudaStream_t stream)
+{
+    int32_t* dIds = static_cast<int32_t*>(r.scratchIds.ensure(std::max<uint64_t>(n, 1) * 4));
+    if (n == 0) {
+        return dIds;
+    }
+    if (!queryBytes || !queryOffsets) {
+        fail(MEMB_B200_ERR_ARGUMENT, "null query buffer");
+    }
+    const uint64_t base = queryOffsets[0];
+    const uint64_t bytes = queryOffsets[n] - base;
+    char* dQuery = static_cast<char*>(r.scratchQuery.ensure(std::max<uint64_t>(bytes, 1)));
+    uint64_t* dOffsets = static_cast<uint64_t*>(r.scratchOffsets.ensure((n + 1) * 8));
+    CUDA_CHECK(cudaMemcpyAsync(dQuery, queryBytes + base, bytes, cudaMemcpyHostToDevice, stream));
+    CUDA_CHECK(cudaMemcpyAsync(dOffsets, queryOffsets, (n + 1) * 8, cudaMemcpyHostToDevice, stream));
+    // offsets are relative to the blob start; the kernel sees the blob from `base`
+    launchResolve(r, dQuery - base, dOffsets, n, dIds, stream);
+    return dIds;
+}
+
+// Decodes n rows of a reader/union into `out` (host or device), in passes when
+// the result has to be staged for a host buffer.
+template <class Launch>
+void decodeTo(memb_b200_reader& r, uint64_t n, uint64_t rowFloats, float* out, memb_b200_mem_kind outKind,
+              cudaStream_t stream, Launch launch)
+{
+    if (n == 0 || rowFloats == 0) {
+        return;
+    }
+    if (!out) {
+        fail(MEMB_B200_ERR_ARGUMENT, "null output buffer");
+    }
+    if (outKind == MEMB_B200_DEVICE) {
+        launch(uint64_t(0), n, out);
+        return;
+    }
+    const uint64_t pass = rowsPerPass(rowFloats);
+    float* dOut = static_cast<float*>(r.scratchOut.ensure(std::min(n, pass) * rowFloats * 4));
+    for (uint64_t first = 0; first < n; first += pass) {
+        const uint64_t count = std::min(pass, n - first);
+        launch(first, count, dOut);
+        CUDA_CHECK(cudaMemcpyAsync(out + first * rowFloats, dOut, count * rowFloats * 4, cudaMemcpyDeviceToHost,
+                                   stream));
+        CUDA_CHECK(cudaStreamSynchronize(stream));
+    }
+}
+
+const int32_t* idsOnDevice(memb_b200_reader& r, const int32_t* ids, memb_b200_mem_kind kind, uint64_t count,
+                           cudaStream_t stream)
+{
+    if (count == 0) {
+        return ids;
+    }
+    if (!ids) {
+        fail(MEMB_B200_ERR_ARGUMENT, "null ids buffer");
+    }
+    if (kind == MEMB_B200_DEVICE) {
+        return ids;
+    }
+    int32_t* dIds = static_cast<int32_t*>(r.scratchIds.ensure(count * 4));
+    CUDA_CHECK(cudaMemcpyAsync(dIds, ids, count * 4, cudaMemcpyHostToDevice, stream));
+    return dIds;
+}
+
+}  // namespace
+
+extern "C" {
+
+memb_b200_status memb_b200_resolve(memb_b200_reader* reader, const char* query_bytes, const uint64_t* query_offsets,
+                                   uint64_t n, int32_t* ids_host)
+{
+    return guarded([&] {
+        if (!reader || (n && !ids_host)) {
+            fail(MEMB_B200_ERR_ARGUMENT, "resolve: null argument");
+        }
+        DeviceGuard guard(reader->device);
+        std::lock_guard<std::mutex> lock(reader->mutex);
+        const int32_t* dIds = resolveToDevice(*reader, query_bytes, query_offsets, n, reader->stream);
+        if (n) {
+            CUDA_CHECK(cudaMemcpyAsync(ids_host, dIds, n * 4, cudaMemcpyDeviceToHost, reader->stream));
+        }
+        CUDA_CHECK(cudaStreamSynchronize(reader->stream));
+    });
+}
+
+memb_b200_status memb_b200_lookup_words(memb_b200_reader* reader, const char* query_bytes,
+                                        const uint64_t* query_offsets, uint64_t n, float* out_host)
+{
+    return guarded([&] {
+        if (!reader) {
+            fail(MEMB_B200_ERR_ARGUMENT, "lookup_words: null reader");
+        }
+        DeviceGuard guard(reader->device);
+        std::lock_guard<std::mutex> lock(reader->mutex);
+        memb_b200_reader& r = *reader;
+        const int32_t* dIds = resolveToDevice(r, query_bytes, query_offsets, n, r.stream);
+        const uint32_t dim = r.file->dim;
+        decodeTo(r, n, dim, out_host, MEMB_B200_HOST, r.stream, [&](uint64_t first, uint64_t count, float* dOut) {
+            K::OutputSpec o{dOut, dim, 0, 1.0f};
+            launchDecode(r, dIds + first, 0, count, o, K::EPI_WRITE, r.stream);
+        });
+        CUDA_CHECK(cudaStreamSynchronize(r.stream));
+    });
+}
+
+memb_b200_status memb_b200_decode_ids(memb_b200_reader* reader, const int32_t* ids, memb_b200_mem_kind ids_kind,
+                                      uint64_t n, float* out, memb_b200_mem_kind out_kind, void* stream)
+{
+    return guarded([&] {
+        if (!reader) {
+            fail(MEMB_B200_ERR_ARGUMENT, "decode_ids: null reader");
+        }
+        DeviceGuard guard(reader->device);
+        memb_b200_reader& r = *reader;
+        const uint32_t dim = r.file->dim;
+        const bool async = ids_kind == MEMB_B200_DEVICE && out_kind == MEMB_B200_DEVICE;
+        cudaStream_t s = out_kind == MEMB_B200_DEVICE ? static_cast<cudaStream_t>(stream) : r.stream;
+        std::unique_lock<std::mutex> lock(r.mutex, std::defer_lock);
+        if (!async) {
+            lock.lock();
+        }
+        const int32_t* dIds = idsOnDevice(r, ids, ids_kind, n, s);
+        decodeTo(r, n, dim, out, out_kind, s, [&](uint64_t first, uint64_t count, float* dOut) {
+            K::OutputSpec o{dOut, dim, 0, 1.0f};
+            launchDecode(r, dIds + first, 0, count, o, K::EPI_WRITE, s);
+        });
+        if (!async) {
+            CUDA_CHECK(cudaStreamSynchronize(s));
+        }
+    });
+}
+
+memb_b200_status memb_b200_decode_range(memb_b200_reader* reader, uint64_t row_begin, uint64_t row_end, float* out,
+                                        memb_b200_mem_kind out_kind, void* stream)
+{
+    return guarded([&] {
+        if (!reader) {
+            fail(MEMB_B200_ERR_ARGUMENT, "decode_range: null reader");
+        }
+        if (row_begin > row_end || row_end > reader->file->rows) {
+            fail(MEMB_B200_ERR_ARGUMENT, "decode_range: rows out of range");
+        }
+        DeviceGuard guard(reader->device);
+        memb_b200_reader& r = *reader;
+        const uint32_t dim = r.file->dim;
+        const bool async = out_kind == MEMB_B200_DEVICE;
+        cudaStream_t s = async ? static_cast<cudaStream_t>(stream) : r.stream;
+        std::unique_lock<std::mutex> lock(r.mutex, std::defer_lock);
+        if (!async) {
+            lock.lock();
+        }
+        decodeTo(r, row_end - row_begin, dim, out, out_kind, s, [&](uint64_t first, uint64_t count, float* dOut) {
+            K::OutputSpec o{dOut, dim, 0, 1.0f};
+            launchDecode(r, nullptr, static_cast<uint32_t>(row_begin + first), count, o, K::EPI_WRITE, s);
+        });
+        if (!async) {
+            CUDA_CHECK(cudaStreamSynchronize(s));
+        }
+    });
+}
+
+memb_b200_status memb_b200_union_decode_ids(memb_b200_reader* const* readers, uint32_t num_readers,
+                                            memb_b200_union_mode mode, const int32_t* ids,
+                                            memb_b200_mem_kind ids_kind, uint64_t n, float* out,
+                                            memb_b200_mem_kind out_kind, void* stream)
+{
+    return guarded([&] {
+        if (!readers) {
+            fail(MEMB_B200_ERR_ARGUMENT, "union_decode_ids: null readers");
+        }
+        const uint64_t unionDim = unionDimOf(readers, num_readers, mode);
+        memb_b200_reader& r = *readers[0];
+        DeviceGuard guard(r.device);
+        const bool async = ids_kind == MEMB_B200_DEVICE && out_kind == MEMB_B200_DEVICE;
+        cudaStream_t s = out_kind == MEMB_B200_DEVICE ? static_cast<cudaStream_t>(stream) : r.stream;
+        std::unique_lock<std::mutex> lock(r.mutex, std::defer_lock);
+        if (!async) {
+            lock.lock();
+        }
+        const int32_t* dIds = idsOnDevice(r, ids, ids_kind, n * num_readers, s);
+        decodeTo(r, n, unionDim, out, out_kind, s, [&](uint64_t first, uint64_t count, float* dOut) {
+            launchUnion(readers, num_readers, mode, dIds, n, first, count, dOut, unionDim, s);
+        });
+        if (!async) {
+            CUDA_CHECK(cudaStreamSynchronize(s));
+        }
+    });
+}
+
+memb_b200_status memb_b200_union_lookup_words(memb_b200_reader* const* readers, uint32_t num_readers,
+                                              memb_b200_union_mode mode, const char* query_bytes,
+                                              const uint64_t* query_offsets, uint64_t n, float* out_host)
+{
+    return guarded([&] {
+        if (!readers) {
+            fail(MEMB_B200_ERR_ARGUMENT, "union_lookup_words: null readers");
+        }
+        const uint64_t unionDim = unionDimOf(readers, num_readers, mode);
+        memb_b200_reader& r = *readers[0];
+        DeviceGuard guard(r.device);
+        std::lock_guard<std::mutex> lock(r.mutex);
+        if (n == 0) {
+            return;
+        }
+        if (!query_bytes || !query_offsets) {
+            fail(MEMB_B200_ERR_ARGUMENT, "null query buffer");
+        }
+        // one upload of the query text, one resolve per reader (each has its own vocabulary)
+        const uint64_t base = query_offsets[0];
+        const uint64_t bytes = query_offsets[n] - base;
+        char* dQuery = static_cast<char*>(r.scratchQuery.ensure(std::max<uint64_t>(bytes, 1)));
+        uint64_t* dOffsets = static_cast<uint64_t*>(r.scratchOffsets.ensure((n + 1) * 8));
+        int32_t* dIds = static_cast<int32_t*>(r.scratchIds.ensure(n * num_readers * 4));
+        CUDA_CHECK(cudaMemcpyAsync(dQuery, query_bytes + base, bytes, cudaMemcpyHostToDevice, r.stream));
+        CUDA_CHECK(cudaMemcpyAsync(dOffsets, query_offsets, (n + 1) * 8, cudaMemcpyHostToDevice, r.stream));
+        for (uint32_t k = 0; k < num_readers; ++k) {
+            launchResolve(*readers[k], dQuery - base, dOffsets, n, dIds + k * n, r.stream);
+        }
+        decodeTo(r, n, unionDim, out_host, MEMB_B200_HOST, r.stream,
+                 [&](uint64_t first, uint64_t count, float* dOut) {
+                     launchUnion(readers, num_readers, mode, dIds, n, first, count, dOut, unionDim, r.stream);
+                 });
+        CUDA_CHECK(cudaStreamSynchronize(r.stream));
+    });
+}
+
+memb_b200_status memb_b200_host_alloc(size_t bytes, void** ptr)
+{
+    return guarded([&] {
+        if (!ptr) {
+            fail(MEMB_B200_ERR_ARGUMENT, "host_alloc: null argument");
+        }
+        *ptr = nullptr;
+        CUDA_CHECK(cudaHostAlloc(ptr, std::max<size_t>(bytes, 1), cudaHostAllocPortable));
+    });
+}
+
+void memb_b200_host_free(void* ptr)
+{
+    if (ptr) {
+        cudaFreeHost(ptr);
+    }
+}
+
+// ---- Builder ----
+struct memb_b200_builder {
+    Builder impl;
+    memb_b200_builder(size_t dim, const std::string& name, size_t bits) : impl(dim, name, bits) {}
+};
+
+memb_b200_status memb_b200_builder_create(uint64_t dim, const char* storage_name, uint64_t bits_per_weight,
+                                          memb_b200_builder** out)
+{
+    const memb_b200_status st = guarded([&] {
+        if (!storage_name || !out) {
+            fail(MEMB_B200_ERR_ARGUMENT, "builder_create: null argument");
+        }
+        *out = nullptr;
+        try {
+            *out = new memb_b200_builder(dim, storage_name, bits_per_weight);
+        } catch (const std::runtime_error& e) {
+            fail(MEMB_B200_ERR_UNSUPPORTED, e.what());
+        }
+    });
+    return st;
+}
+
+void memb_b200_builder_destroy(memb_b200_builder* builder)
+{
+    delete builder;
+}
+
+memb_b200_status memb_b200_builder_add_word(memb_b200_builder* builder, const char* word, size_t word_len,
+                                            const float* values, uint64_t count)
+{
+    return guarded([&] {
+        if (!builder || !word || (count && !values)) {
+            fail(MEMB_B200_ERR_ARGUMENT, "builder_add_word: null argument");
+        }
+        try {
+            builder->impl.addWord(std::string(word, word_len), values, count);
+        } catch (const std::runtime_error& e) {
+            fail(MEMB_B200_ERR_BUILDER, e.what());
+        }
+    });
+}
+
+memb_b200_status memb_b200_builder_add_words(memb_b200_builder* builder, const char* blob, const uint64_t* offsets,
+                                             uint64_t n, const float* matrix)
+{
+    return guarded([&] {
+        if (!builder || (n && (!blob || !offsets || !matrix))) {
+            fail(MEMB_B200_ERR_ARGUMENT, "builder_add_words: null argument");
+        }
+        try {
+            builder->impl.addWords(blob, offsets, n, matrix);
+        } catch (const std::runtime_error& e) {
+            fail(MEMB_B200_ERR_BUILDER, e.what());
+        }
+    });
+}
+
+memb_b200_status memb_b200_builder_save(memb_b200_builder* builder, const char* path, unsigned num_threads)
+{
+    return guarded([&] {
+        if (!builder || !path) {
+            fail(MEMB_B200_ERR_ARGUMENT, "builder_save: null argument");
+        }
+        builder->impl.save(path, num_threads);
+    });
+}
+
+const char* memb_b200_available_compression_strategies(void)
+{
+    return "full\0uniform\0trained\0";
+}
+
+}  // extern "C"
