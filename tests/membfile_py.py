@@ -1,0 +1,216 @@
+"""Pure-Python writer of memb files (test infrastructure).
+
+An independent second implementation of the wire format — written from the six
+schemas (/root/reference/src/flatbuffers/*.fbs) and the public FlatBuffers binary
+layout — so that the C++ parser is not only ever tested against the C++ writer,
+and so that tests can hand-craft files the Builder can never emit (a 16-bit
+prefix code, a one-symbol code, omitted default fields, overlapping rows, ...).
+"""
+import struct
+
+import numpy as np
+
+
+class _Writer:
+    """Front-to-back FlatBuffers layout: parents first, children after, every
+    uoffset patched once its target is placed (targets are always forward)."""
+
+    def __init__(self):
+        self.buf = bytearray()
+
+    def align(self, n):
+        while len(self.buf) % n:
+            self.buf.append(0)
+
+    def patch_offset(self, at, target):
+        struct.pack_into("<I", self.buf, at, target - at)
+
+    def vector(self, array, elem_align=4):
+        array = np.ascontiguousarray(array)
+        self.align(max(4, elem_align))
+        pos = len(self.buf)
+        self.buf += struct.pack("<I", len(array))
+        self.buf += array.tobytes()
+        return pos
+
+    def string(self, data):
+        self.align(4)
+        pos = len(self.buf)
+        self.buf += struct.pack("<I", len(data)) + bytes(data) + b"\0"
+        return pos
+
+    def table(self, fields):
+        """fields: list of (id, fmt, value) with fmt in {'B','I','f'} for scalars or
+        'O' for a child; a child value is a callable emitting the child and
+        returning its position.  Fields given as None are omitted (= default)."""
+        fields = [f for f in fields if f is not None]
+        nslots = max([f[0] for f in fields], default=-1) + 1
+        sizes = {"B": 1, "I": 4, "f": 4, "O": 4}
+        # inline layout: soffset, then 4-byte fields, then 1-byte fields
+        layout, cursor = {}, 4
+        for fid, fmt, _ in sorted(fields, key=lambda f: -sizes[f[1]]):
+            layout[fid] = cursor
+            cursor += sizes[fmt]
+        table_size = cursor
+        vt_size = 4 + 2 * nslots
+        # place the vtable so that the table after it is 4-aligned
+        while (len(self.buf) + vt_size) % 4:
+            self.buf.append(0)
+        vt_pos = len(self.buf)
+        self.buf += struct.pack("<HH", vt_size, table_size)
+        for slot in range(nslots):
+            self.buf += struct.pack("<H", layout.get(slot, 0))
+        pos = len(self.buf)
+        self.buf += struct.pack("<i", pos - vt_pos)
+        self.buf += bytes(table_size - 4)
+        children = []
+        for fid, fmt, value in fields:
+            at = pos + layout[fid]
+            if fmt == "O":
+                children.append((at, value))
+            else:
+                struct.pack_into("<" + fmt, self.buf, at, value)
+        for at, emit in children:
+            self.patch_offset(at, emit())
+        return pos
+
+    def table_vector(self, emitters):
+        self.align(4)
+        pos = len(self.buf)
+        self.buf += struct.pack("<I", len(emitters)) + bytes(4 * len(emitters))
+        for i, emit in enumerate(emitters):
+            self.patch_offset(pos + 4 + 4 * i, emit())
+        return pos
+
+
+def _finish(storage_type, dim, emit_storage):
+    w = _Writer()
+    w.buf += bytes(4) + b"memb"
+    root = w.table([(0, "B", storage_type), (1, "O", emit_storage(w)), (2, "I", dim) if dim else None])
+    struct.pack_into("<I", w.buf, 0, root)
+    return bytes(w.buf)
+
+
+def canonical_codes(lengths):
+    """(code, length) per symbol for lengths sorted ascending (src/prefix_code.cpp:5-22)."""
+    codes, code, bits = [], 0, 0
+    for length in lengths:
+        while bits < length:
+            bits += 1
+            code <<= 1
+        codes.append(code & 0xffff)
+        code += 1
+    return codes
+
+
+def size_offsets_from_lengths(lengths):
+    """Serialised length table (src/huffman_encoder.cpp:100-117): one entry pushed each
+    time the code length grows by one, plus the final key count."""
+    out, current = [], 0
+    for i, length in enumerate(lengths):
+        while current < length:
+            out.append(i)
+            current += 1
+    out.append(len(lengths))
+    return out
+
+
+def pack_row(symbols, code_of, len_of):
+    """MSB-first concatenation of the codes, zero padded to a byte (src/bit_stream.h:18-34)."""
+    bits = []
+    for s in symbols:
+        code, length = code_of[s], len_of[s]
+        bits.extend((code >> k) & 1 for k in range(length - 1, -1, -1))
+    while len(bits) % 8:
+        bits.append(0)
+    if not bits:
+        return b""
+    return np.packbits(np.array(bits, np.uint8)).tobytes()
+
+
+def write_trained(path, words, symbol_rows, keys, lengths, centroids, dim=None, row_order=None, tail=b""):
+    """words: list of bytes in ANY order (they are sorted here like the compressor does,
+    src/trained_compression.cpp:73-79); symbol_rows[i] = the dim symbols (key values)
+    of words[i]; keys/lengths: the prefix code, lengths ascending.  Rows are packed in
+    `row_order` (default: insertion order), offsets sorted by word.  `tail` is appended
+    to packed_values (junk after the last row must not matter)."""
+    keys = [int(k) for k in keys]
+    lengths = [int(v) for v in lengths]
+    codes = canonical_codes(lengths)
+    code_of = {k: c for k, c in zip(keys, codes)}
+    len_of = {k: v for k, v in zip(keys, lengths)}
+    dim = len(symbol_rows[0]) if dim is None else dim
+    order = list(range(len(words))) if row_order is None else list(row_order)
+    packed, value_offset = bytearray(), {}
+    for i in order:
+        value_offset[i] = len(packed)
+        packed += pack_row(symbol_rows[i], code_of, len_of)
+    packed += tail
+    by_word = sorted(range(len(words)), key=lambda i: words[i])
+    packed_words, word_offsets = bytearray(), []
+    for i in by_word:  # text in sorted order, every word with its NUL (trained_compression.cpp:85-90)
+        word_offsets.append(len(packed_words))
+        packed_words += words[i] + b"\0"
+    wo = np.array(word_offsets, np.uint32)
+    vo = np.array([value_offset[i] for i in by_word], np.uint32)
+    so = np.array(size_offsets_from_lengths(lengths), np.uint32)
+
+    def storage(w):
+        def decoder():
+            return w.table([(0, "O", lambda: w.vector(np.array(keys, np.uint8), 1)), (1, "O", lambda: w.vector(so))])
+
+        def clusterizer():
+            return w.table([(0, "O", lambda: w.vector(np.asarray(centroids, np.float32)))])
+
+        return lambda: w.table([
+            (0, "O", lambda: w.vector(wo)), (1, "O", lambda: w.vector(vo)),
+            (2, "O", lambda: w.string(bytes(packed_words))),
+            (3, "O", lambda: w.vector(np.frombuffer(bytes(packed), np.uint8), 1)),
+            (4, "O", decoder), (5, "O", clusterizer)])
+
+    data = _finish(3, dim, storage)
+    with open(path, "wb") as f:
+        f.write(data)
+    return [words[i] for i in by_word]
+
+
+def write_uniform(path, words, mins, maxs, values, levels, omit_defaults=True):
+    """values: (n, dim) uint8; nodes sorted by word like CreateVectorOfSortedTables.
+    A scalar equal to its default (0.0) is omitted like the flatbuffers builder does."""
+    by_word = sorted(range(len(words)), key=lambda i: words[i])
+    values = np.asarray(values, np.uint8)
+
+    def storage(w):
+        def node(i):
+            def vec():
+                mn, mx = float(mins[i]), float(maxs[i])
+                return w.table([
+                    None if (omit_defaults and mn == 0.0) else (0, "f", mn),
+                    None if (omit_defaults and mx == 0.0) else (1, "f", mx),
+                    (2, "O", lambda: w.vector(values[i], 1))])
+
+            return lambda: w.table([(0, "O", lambda: w.string(words[i])), (1, "O", vec)])
+
+        return lambda: w.table([(0, "O", lambda: w.table_vector([node(i) for i in by_word])),
+                                None if (omit_defaults and levels == 0) else (1, "B", levels)])
+
+    data = _finish(2, values.shape[1], storage)
+    with open(path, "wb") as f:
+        f.write(data)
+    return [words[i] for i in by_word]
+
+
+def write_full(path, words, matrix):
+    by_word = sorted(range(len(words)), key=lambda i: words[i])
+    matrix = np.asarray(matrix, np.float32)
+
+    def storage(w):
+        def node(i):
+            return lambda: w.table([(0, "O", lambda: w.string(words[i])), (1, "O", lambda: w.vector(matrix[i]))])
+
+        return lambda: w.table([(0, "O", lambda: w.table_vector([node(i) for i in by_word]))])
+
+    data = _finish(1, matrix.shape[1], storage)
+    with open(path, "wb") as f:
+        f.write(data)
+    return [words[i] for i in by_word]
