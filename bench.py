@@ -1,0 +1,453 @@
+"""bench.py — the headline measurement of the batched embedding lookup.
+
+    python bench.py --gpus N --steps K --warmup W            (N>1: launched by torchrun)
+    python bench.py --impl reference --gpus N --steps K --warmup W
+
+Workload (BASELINE.json configs[1]): GloVe-840B-shaped synthetic table, 2.2 M x 300,
+`trained` 4-bit (k-means codebook + Huffman), one step = one batched lookup of 1 M
+random row ids (uniform with replacement, seed 4) -> (1 M, 300) fp32.  At N>1 every
+rank holds a replica of the compressed table and decodes its own 1 M-id batch
+(queries shard, no data-path collective): weak scaling.
+
+One JSON line on stdout (rank 0).  `value` = rows/s with ids and output resident in
+HBM; `e2e` = the same lookup through the C ABI with HOST buffers (pinned ids in,
+pinned fp32 rows out), copies inside the timed region.  `roofline` is for the
+dominant kernel (trained_decode_kernel); `cpu_baseline` times the CPU oracle (whose
+Huffman decode is the reference's own header when oracle/_ref was built) on the host
+cores.  The oracle is only ever the thing compared against / the CPU baseline here.
+"""
+import argparse
+import ctypes
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "decoded rows/sec (fp32 output GB/s vs HBM peak) of the batched embedding lookup"
+UNIT = "rows/s"
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=200)
+    p.add_argument("--warmup", type=int, default=5)
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--rows", type=int, default=2_200_000, help="vocabulary rows of the synthetic table")
+    p.add_argument("--dim", type=int, default=300)
+    p.add_argument("--bits", type=int, default=4)
+    p.add_argument("--batch", type=int, default=1_000_000, help="row ids per step and per GPU")
+    p.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (0 = auto)")
+    p.add_argument("--no-extra", action="store_true", help="skip the secondary measurements")
+    p.add_argument("--cache-dir", default=os.environ.get("MEMB_B200_BENCH_DIR", "/tmp/memb_b200_bench"))
+    return p.parse_args()
+
+
+# ------------------------------------------------------------- workload ----
+def table_path(args):
+    return os.path.join(args.cache_dir, "glove_shape_%d_x_%d_trained%d.bin" % (args.rows, args.dim, args.bits))
+
+
+def build_table(args):
+    """Synthetic GloVe-840B-shaped file through the repo's Builder (the memb_converter
+    equivalent): N(0,1) float32 vectors (PCG64 seed 3 per chunk), unique words in
+    shuffled insertion order.  Cached on disk; returns build seconds (0 when cached)."""
+    path = table_path(args)
+    if os.path.exists(path):
+        return 0.0
+    import memb_b200
+    from concurrent.futures import ThreadPoolExecutor
+
+    t0 = time.time()
+    os.makedirs(args.cache_dir, exist_ok=True)
+    rows, dim = args.rows, args.dim
+    matrix = np.empty((rows, dim), np.float32)
+    chunks = max(1, min(32, os.cpu_count() or 1))
+    bounds = np.linspace(0, rows, chunks + 1).astype(np.int64)
+
+    def fill(i):
+        rng = np.random.Generator(np.random.PCG64([3, i]))
+        rng.standard_normal(out=matrix[bounds[i]:bounds[i + 1]], dtype=np.float32)
+
+    with ThreadPoolExecutor(chunks) as pool:
+        list(pool.map(fill, range(chunks)))
+    order = np.random.Generator(np.random.PCG64(33)).permutation(rows)
+    words = ["w%x" % i for i in order]
+    builder = memb_b200.Builder(dim, "trained", args.bits)
+    builder.add_words(words, matrix)
+    tmp = path + ".tmp%d" % os.getpid()
+    builder.save(tmp)
+    os.replace(tmp, path)
+    return time.time() - t0
+
+
+def batch_ids(args, rank):
+    rng = np.random.Generator(np.random.PCG64([4, rank]))
+    return rng.integers(0, args.rows, args.batch, dtype=np.int64).astype(np.int32)
+
+
+# ------------------------------------------------------------- oracle (CPU baseline only) ----
+class CpuOracle:
+    """ctypes view of oracle/_ref/liboracle_ref.so (reference Huffman headers) or, when
+    that was not built, oracle/liboracle.so (the restatement)."""
+
+    def __init__(self, path, threads=0):
+        ref = os.path.join(ROOT, "oracle", "_ref", "liboracle_ref.so")
+        port = os.path.join(ROOT, "oracle", "liboracle.so")
+        self.uses_reference_codec = os.path.exists(ref)
+        lib = ctypes.CDLL(ref if self.uses_reference_codec else port)
+        lib.oracle_open.restype = ctypes.c_void_p
+        lib.oracle_open.argtypes = [ctypes.c_char_p, ctypes.c_uint64]
+        lib.oracle_threads.restype = ctypes.c_uint64
+        lib.oracle_threads.argtypes = [ctypes.c_void_p]
+        lib.oracle_batch_ids.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p]
+        lib.oracle_close.argtypes = [ctypes.c_void_p]
+        self.lib = lib
+        self.h = lib.oracle_open(path.encode(), threads)
+        if not self.h:
+            raise RuntimeError("oracle cannot open " + path)
+        self.threads = int(lib.oracle_threads(self.h))
+
+    def batch_ids(self, ids, out):
+        self.lib.oracle_batch_ids(self.h, ids.ctypes.data, len(ids), out.ctypes.data)
+
+    def describe(self):
+        codec = ("reference huffman_table_decoder.h/bit_stream_reader.h compiled from /root/reference (oracle/_ref)"
+                 if self.uses_reference_codec else "restated codec (oracle/oracle.cpp)")
+        return "CPU oracle Reader: %s + restated lookup/threading of src/reader.cpp:59-86" % codec
+
+
+def time_cpu(oracle, ids, dim, steps, warmup, budget_s=25.0):
+    """Seconds per pass over `ids` (best and mean over <= steps passes within budget)."""
+    out = np.empty((len(ids), dim), np.float32)
+    for _ in range(warmup):
+        oracle.batch_ids(ids, out)
+    times, start = [], time.perf_counter()
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        oracle.batch_ids(ids, out)
+        times.append(time.perf_counter() - t0)
+        if time.perf_counter() - start > budget_s:
+            break
+    return times, out
+
+
+# ------------------------------------------------------------- clocks ----
+class ClockSampler:
+    """Samples SM clock and throttle reasons DURING the timed region (NVML, ~every 5 ms)."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+               0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting", 0x100: "display_clock_setting"}
+
+    def __init__(self, device_index):
+        self.samples, self.reasons, self.power = [], set(), []
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            index = device_index
+            if visible:
+                entry = visible.split(",")[device_index]
+                self.handle = (pynvml.nvmlDeviceGetHandleByUUID(entry) if entry.startswith("GPU-")
+                               else pynvml.nvmlDeviceGetHandleByIndex(int(entry)))
+            else:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.nvml = pynvml
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)
+        except Exception as exc:  # noqa: BLE001
+            self.nvml = None
+            self.error = str(exc)
+
+    def _loop(self):
+        nv = self.nvml
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM))
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+                self.power.append(nv.nvmlDeviceGetPowerUsage(self.handle) / 1000.0)
+            except Exception:  # noqa: BLE001
+                pass
+            self._stop.wait(0.005)
+
+    def start(self):
+        if self.nvml:
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
+
+    def stop(self):
+        if self._thread:
+            self._stop.set()
+            self._thread.join()
+        if not self.nvml or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0,
+                    "note": getattr(self, "error", "no samples")}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples),
+                "power_w_max": max(self.power) if self.power else None}
+
+
+def workload_config(args, extra=None):
+    config = {
+        "workload": "configs[1]: GloVe-840B-shaped synthetic %d x %d, trained %d-bit; random batched lookup of %d "
+                    "row ids per step per GPU" % (args.rows, args.dim, args.bits, args.batch),
+        "rows": args.rows, "dim": args.dim, "bits_per_weight": args.bits, "batch_ids": args.batch,
+        "ids": "uniform with replacement, PCG64 seed [4, rank]",
+        "l2": "inputs larger than L2: every step writes %.0f MB and gathers from a %s compressed table; no flush "
+              "needed" % (args.batch * args.dim * 4 / 1e6, "~290 MB" if args.rows >= 2_000_000 else "small"),
+        "parallelism": "replicated table, queries sharded by rank, no collective",
+    }
+    config.update(extra or {})
+    return config
+
+
+# ------------------------------------------------------------- reference arm ----
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # under torchrun only rank 0 measures the CPU implementation
+    build_table(args)
+    oracle = CpuOracle(table_path(args), threads=0)
+    ids = batch_ids(args, 0)
+    # bounded sample: at most ~25 s per phase; a step is the full batch unless it is too slow
+    sample = len(ids)
+    t0 = time.perf_counter()
+    probe = np.empty((min(sample, 20000), args.dim), np.float32)
+    oracle.batch_ids(ids[:len(probe)], probe)
+    per_row = (time.perf_counter() - t0) / len(probe)
+    budget_rows = int(60.0 / max(per_row, 1e-12) / max(args.steps + args.warmup, 1))
+    if budget_rows < sample:
+        sample = max(1024, budget_rows)
+    times, _ = time_cpu(oracle, ids[:sample], args.dim, args.steps, args.warmup, budget_s=120.0)
+    ms = 1e3 * float(np.mean(times))
+    value = sample / (ms / 1e3)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": len(times), "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8 symbols -> f32 codebook gather", "data": "synthetic",
+        "config": workload_config(args),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": oracle.threads, "kind": "port",
+                         "codec": "reference headers" if oracle.uses_reference_codec else "restated",
+                         "sample": "%d of the %d ids of one step, %d timed passes; %s; host has %d logical cpus"
+                                   % (sample, len(ids), len(times), oracle.describe(), os.cpu_count() or 0)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "output_gb_per_s": value * args.dim * 4 / 1e9,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------- B200 arm ----
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy, kernel timed alone)"
+    except Exception:  # noqa: BLE001
+        return 6650.0, "fallback of B200_PROFILING.md (MEASURED_PEAKS.json absent)"
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    import memb_b200
+    from memb_b200 import _memb
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch with torchrun --nproc-per-node %d" %
+                         (args.gpus, world, args.gpus))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: there is no CPU path in memb_b200")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    build_s = build_table(args) if rank == 0 else 0.0
+    barrier()
+
+    t0 = time.perf_counter()
+    reader = memb_b200.Reader(table_path(args), device=local)
+    open_s = time.perf_counter() - t0
+    stats = reader.load_stats()
+    impl = reader._impl
+    rows, dim, n = reader.rows, reader.dim, args.batch
+
+    ids_host = torch.from_numpy(batch_ids(args, rank)).pin_memory()
+    ids_dev = ids_host.to(device)
+    out_dev = torch.empty((n, dim), dtype=torch.float32, device=device)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step_device():
+        impl.decode_ids_into(ids_dev.data_ptr(), True, n, out_dev.data_ptr(), True, stream)
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local)
+    launches0 = _memb.launch_count()
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.start()
+    start.record()
+    for _ in range(args.steps):
+        step_device()
+    stop.record()
+    barrier()
+    clocks = sampler.stop()
+    launches = _memb.launch_count() - launches0
+    ms_total = max_over_ranks(start.elapsed_time(stop))
+    ms_step = ms_total / args.steps
+    value = world * n / (ms_step / 1e3)
+
+    # ---- e2e: the C-ABI call with HOST buffers (pinned), H2D ids + D2H rows inside the timed region ----
+    out_host = torch.empty((n, dim), dtype=torch.float32).pin_memory()
+    e2e_steps = args.e2e_steps or max(3, min(args.steps, 20))
+
+    def step_host():
+        impl.decode_ids_into(ids_host.data_ptr(), False, n, out_host.data_ptr(), False, 0)
+
+    step_host()
+    step_host()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_host()  # returns when out_host is complete
+    torch.cuda.synchronize()
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / e2e_steps
+    e2e_value = world * n / (e2e_ms / 1e3)
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- rank 0: parity spot check, roofline, cpu baseline, extras ----
+    peak, peak_source = measured_peak()
+    payload_per_row = stats["payload_bytes"] / rows
+    bytes_per_row = 4 * dim + payload_per_row + 4 + 4  # fp32 out + compressed row + value_offset + id
+    achieved = n * bytes_per_row / (ms_step / 1e3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "trained_decode_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_source,
+                "algorithmic_bytes_per_row": bytes_per_row,
+                "write_only_frac": n * 4 * dim / (ms_step / 1e3) / 1e9 / peak,
+                "launch_ms": ms_step}
+
+    oracle = CpuOracle(table_path(args), threads=0)
+    sample = min(n, 200_000) if (os.cpu_count() or 1) < 32 else n
+    cpu_times, cpu_out = time_cpu(oracle, ids_host.numpy()[:sample], dim, steps=5, warmup=1, budget_s=20.0)
+    parity = bool(np.array_equal(cpu_out.view(np.uint32), out_host.numpy()[:sample].view(np.uint32)))
+    cpu_value = sample / float(np.min(cpu_times))
+    cpu_baseline = {"value": cpu_value, "unit": UNIT, "cores": oracle.threads, "kind": "port",
+                    "codec": "reference headers" if oracle.uses_reference_codec else "restated",
+                    "sample": "first %d ids of the step's batch, best of %d passes; %s; host has %d logical cpus"
+                              % (sample, len(cpu_times), oracle.describe(), os.cpu_count() or 0)}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8 symbols -> f32 codebook gather", "data": "synthetic",
+        "config": workload_config(args),
+        "output_gb_per_s": value * dim * 4 / 1e9,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 4, "d2h_bytes_per_step": n * dim * 4,
+                "ms_per_step": e2e_ms, "steps": e2e_steps,
+                "api": "memb_b200_decode_ids(host ids -> host rows) via _memb.Reader.decode_ids_into"},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": roofline,
+        "cpu_baseline": cpu_baseline,
+        "parity_vs_oracle": parity,
+        "load": {"table_build_s": build_s, "open_s": open_s, "parse_ms": stats["parse_ms"],
+                 "upload_ms": stats["upload_ms"], "prepare_ms": stats["prepare_ms"],
+                 "device_bytes": stats["device_bytes"], "payload_bytes": stats["payload_bytes"],
+                 "max_code_len": stats["max_code_len"], "lut_bits": stats["lut_bits"],
+                 "lut_replicas": stats["lut_replicas"], "codebook_size": stats["codebook_size"]},
+    }
+    if not args.no_extra:
+        line["extra"] = extras(args, reader, device, peak)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    print(json.dumps(line), flush=True)
+    if not parity:
+        raise SystemExit("bench: GPU rows differ from the oracle")
+
+
+def extras(args, reader, device, peak):
+    """Secondary measurements (rank 0, one GPU): full-vocabulary decode (configs[2] at
+    G=1) and the words entry point end to end."""
+    import torch
+
+    impl = reader._impl
+    rows, dim = reader.rows, reader.dim
+    out = torch.empty((rows, dim), dtype=torch.float32, device=device)
+    stream = torch.cuda.current_stream().cuda_stream
+    for _ in range(3):
+        impl.decode_range_into(0, rows, out.data_ptr(), True, stream)
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 20
+    torch.cuda.synchronize()
+    start.record()
+    for _ in range(reps):
+        impl.decode_range_into(0, rows, out.data_ptr(), True, stream)
+    stop.record()
+    torch.cuda.synchronize()
+    ms = start.elapsed_time(stop) / reps
+    stats = reader.load_stats()
+    bytes_per_row = 4 * dim + stats["payload_bytes"] / rows + 4
+    result = {"full_vocab_decode": {"rows": rows, "ms": ms, "rows_per_s": rows / (ms / 1e3),
+                                    "roofline_frac": rows * bytes_per_row / (ms / 1e3) / 1e9 / peak}}
+    del out
+    # words entry point: 1M words -> rows, host buffers, through the binding's list[str] API
+    n = min(args.batch, 1_000_000)
+    keys = reader.keys()
+    rng = np.random.Generator(np.random.PCG64(44))
+    words = [keys[i] for i in rng.integers(0, rows, n)]
+    reader.batch_embedding(words[:1000])
+    t0 = time.perf_counter()
+    got = reader.batch_embedding(words)
+    dt = time.perf_counter() - t0
+    result["words_api_e2e"] = {"words": n, "s": dt, "rows_per_s": n / dt,
+                               "note": "Reader.batch_embedding(list[str]) incl. Python str marshalling, H2D, resolve "
+                                       "kernel, decode, D2H into a fresh numpy array"}
+    del got
+    return result
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,316 @@
+"""Parity tests proper: the CUDA path, called through the C ABI (ctypes) and
+through the `_memb` binding, against the CPU oracle on the same inputs.
+Bar: bit-exact for row ids, decoded trained rows, full rows and union merges;
+uniform dequant is allowed 1 ulp by the north star — asserted 0 ulp here."""
+import numpy as np
+import pytest
+
+import helpers
+import membfile_py
+from conftest import TEST_VECTORS
+from helpers import bits_equal
+
+pytestmark = pytest.mark.gpu
+
+
+def queries_for(syn, rng, n, miss_fraction=0.05):
+    words = [syn.words[i] for i in rng.integers(0, len(syn.words), n)]
+    for i in rng.integers(0, n, max(1, int(n * miss_fraction))):
+        words[i] = ["", "o", "zzzzzzzz", "w", "é", "w1\0tail", "absent%d" % i][i % 7]
+    return words
+
+
+# ---- the reference's own cases (src/tests.cpp) through the CUDA path ----
+@pytest.mark.parametrize("storage", ["full", "uniform", "trained"])
+def test_reference_builder_cases_on_gpu(abi, oracle, reference_files, storage):
+    reader = abi.open_checked(reference_files[storage])
+    want = oracle.open(reference_files[storage])
+    assert reader.dim == 3 and reader.rows == 6
+    assert reader.keys() == sorted(w.encode() for w, _ in TEST_VECTORS)  # tests.cpp:36-43
+    words = [w for w, _ in TEST_VECTORS] + ["o", "zzz", ""]
+    got = reader.lookup_words(words)
+    assert bits_equal(got, want.batch_embedding(words))
+    for (word, vector), row in zip(TEST_VECTORS, got):
+        assert np.allclose(row, vector, rtol=0.01, atol=0)  # tests.cpp:49
+    assert np.all(got[len(TEST_VECTORS):] == 0.0)  # tests.cpp:53-56
+    assert np.array_equal(reader.resolve(words), want.resolve(words))
+
+
+def test_threaded_decoder_case_on_gpu(abi, oracle, reference_files):
+    """threadedDecoderWorks (tests.cpp:90-113): 1025 words; any partition gives the same bits."""
+    batch = [TEST_VECTORS[i % len(TEST_VECTORS)][0] for i in range(1025)]
+    reader = abi.open_checked(reference_files["trained"])
+    got = reader.lookup_words(batch)
+    assert bits_equal(got, oracle.open(reference_files["trained"], 4).batch_embedding(batch))
+
+
+def test_open_errors_on_gpu(abi, workdir):
+    status, handle = abi.open(str(workdir / "missing_gpu.bin"))
+    assert status == abi.ERR_IO
+    bad = workdir / "bad_gpu.bin"
+    bad.write_bytes(b"0123456789")
+    assert abi.open(str(bad))[0] == abi.ERR_FORMAT
+    import memb_b200
+
+    with pytest.raises(RuntimeError):
+        memb_b200.Reader(str(bad))
+    with pytest.raises(Exception):
+        memb_b200.Reader(str(workdir / "missing_gpu.bin"))
+
+
+# ---- golden codec vectors (reference codec output) through the kernel ----
+def test_golden_codec_vectors_on_gpu(abi, golden, workdir):
+    rng = np.random.default_rng(11)
+    for name in golden["names"]:
+        keys, lens, symbols = golden[name + ".keys"], golden[name + ".lens"], golden[name + ".symbols"]
+        centroids = rng.standard_normal(int(keys.max()) + 1).astype(np.float32)
+        for dim in (len(symbols), 300, 7):
+            rows = len(symbols) // dim
+            sym = symbols[:rows * dim].reshape(rows, dim)
+            words = [("g%04d" % i).encode() for i in range(rows)]
+            path = str(workdir / ("golden_%s_%d.bin" % (name, dim)))
+            membfile_py.write_trained(path, words, sym, keys, lens, centroids, tail=b"\xa5" * 3)
+            reader = abi.open_checked(path)
+            got = reader.decode_range(0, rows)
+            assert bits_equal(got, centroids[sym]), (name, dim)
+            reader.close()
+
+
+# ---- trained: 1..8 bits, ids / words / range, odd sizes ----
+@pytest.mark.parametrize("bits", [1, 2, 3, 4, 5, 6, 7, 8])
+def test_trained_parity_bits_sweep(abi, oracle, synthetic, bits):
+    syn = synthetic("trained", bits, rows=3000, dim=300)
+    reader, want = abi.open_checked(syn.path), oracle.open(syn.path)
+    rng = np.random.default_rng(bits)
+    assert bits_equal(reader.decode_range(0, 3000), want.decode_range(0, 3000))
+    ids = rng.integers(-2, 3002, 5000).astype(np.int32)
+    assert bits_equal(reader.decode_ids(ids), want.batch_ids(ids))
+    words = queries_for(syn, rng, 2000)
+    assert np.array_equal(reader.resolve(words), want.resolve(words))
+    assert bits_equal(reader.lookup_words(words), want.batch_embedding(words))
+    stats = reader.load_stats()
+    assert stats.codebook_size == len(want.codebook()) and stats.max_code_len == want.prefix_code()[2].max()
+
+
+@pytest.mark.parametrize("dim", [1, 3, 4, 31, 32, 33, 64, 100, 301, 768])
+def test_trained_parity_dims(abi, oracle, synthetic, dim):
+    syn = synthetic("trained", 4, rows=700, dim=dim, seed=dim)
+    reader, want = abi.open_checked(syn.path), oracle.open(syn.path)
+    assert bits_equal(reader.decode_range(0, 700), want.decode_range(0, 700))
+    assert bits_equal(reader.decode_range(13, 77), want.decode_range(13, 77))
+
+
+@pytest.mark.parametrize("n", [0, 1, 31, 32, 33, 1023, 1024, 1025])
+def test_batch_sizes(abi, oracle, synthetic, n):
+    syn = synthetic("trained", 6, rows=3000, dim=300)
+    reader, want = abi.open_checked(syn.path), oracle.open(syn.path, 4)
+    rng = np.random.default_rng(n)
+    words = queries_for(syn, rng, n) if n else []
+    got = reader.lookup_words(words)
+    assert got.shape == (n, 300) and bits_equal(got, want.batch_embedding(words))
+    ids = rng.integers(0, 3000, n).astype(np.int32)
+    ids[: n // 2] = ids[n // 2: 2 * (n // 2)]  # duplicates in one batch
+    assert bits_equal(reader.decode_ids(ids), want.batch_ids(ids))
+
+
+def test_trained_edge_codes(abi, oracle, workdir):
+    """Files the Builder cannot emit: one-symbol code (zero-byte rows), 16-bit codes
+    (escape path beyond the device LUT), 255 symbols, rows packed in shuffled order."""
+    rng = np.random.default_rng(2)
+    cases = {
+        "one": ([9], [0]),
+        "two": ([1, 0], [1, 1]),
+        "deep16": (list(range(17)), list(range(1, 17)) + [16]),
+        "wide255": (list(rng.permutation(255)), [7] * 1 + [8] * 254),
+    }
+    for name, (keys, lens) in cases.items():
+        assert sum(2.0 ** -n for n in lens) == 1.0 or len(lens) == 1
+        centroids = rng.standard_normal(max(keys) + 1).astype(np.float32)
+        for dim in (300, 5):
+            rows = 257
+            weights = np.array([2.0 ** -n for n in lens])
+            weights = weights + 0.02  # long codes far more often than a Huffman source would
+            sym = np.array(keys)[rng.choice(len(keys), (rows, dim), p=weights / weights.sum())]
+            words = [("e%03d" % i).encode() for i in rng.permutation(rows)]
+            path = str(workdir / ("edge_%s_%d.bin" % (name, dim)))
+            membfile_py.write_trained(path, words, sym, keys, lens, centroids, row_order=rng.permutation(rows))
+            reader, want = abi.open_checked(path), oracle.open(path)
+            got = reader.lookup_words(words)
+            assert bits_equal(got, centroids[sym]), (name, dim)
+            assert bits_equal(got, want.batch_embedding(words)), (name, dim)
+            reader.close()
+
+
+def test_lut_layouts_do_not_change_results(abi, oracle, synthetic):
+    """GPU analogue of trainedBuilderWorksWithIndirectDecoder (tests.cpp:76-88):
+    every LUT layout / kernel variant decodes the same bits."""
+    syn = synthetic("trained", 8, rows=3000, dim=300)
+    want = oracle.open(syn.path).decode_range(0, 3000)
+    try:
+        for name, value in (("trained_lut_replicas", 1), ("trained_lut_replicas", 32), ("trained_warps", 3),
+                            ("trained_generic", 1)):
+            abi.check(abi.lib.memb_b200_set_option(name.encode(), value))
+            reader = abi.open_checked(syn.path)
+            assert bits_equal(reader.decode_range(0, 3000), want), (name, value)
+            reader.close()
+            abi.check(abi.lib.memb_b200_set_option(name.encode(), 0))
+    finally:
+        for name in ("trained_lut_replicas", "trained_warps", "trained_generic"):
+            abi.lib.memb_b200_set_option(name.encode(), 0)
+
+
+# ---- uniform / full ----
+@pytest.mark.parametrize("bits", [1, 2, 4, 8])
+def test_uniform_parity(abi, oracle, synthetic, bits):
+    syn = synthetic("uniform", bits, rows=3000, dim=300, seed=5)
+    reader, want = abi.open_checked(syn.path), oracle.open(syn.path)
+    rng = np.random.default_rng(bits)
+    assert bits_equal(reader.decode_range(0, 3000), want.decode_range(0, 3000))  # 0 ulp (bar: 1 ulp)
+    words = queries_for(syn, rng, 1500)
+    assert np.array_equal(reader.resolve(words), want.resolve(words))
+    assert bits_equal(reader.lookup_words(words), want.batch_embedding(words))
+
+
+def test_uniform_omitted_fields_and_odd_dim(abi, oracle, workdir):
+    rng = np.random.default_rng(4)
+    rows, dim = 500, 37
+    words = [("u%03d" % i).encode() for i in rng.permutation(rows)]
+    values = rng.integers(0, 256, (rows, dim)).astype(np.uint8)
+    mins = (rng.standard_normal(rows) * 3).astype(np.float32)
+    maxs = mins + rng.random(rows).astype(np.float32) * 5
+    mins[::5] = 0.0
+    maxs[2::9] = 0.0
+    mins[7] = maxs[7] = 1.5  # min == max
+    mins[8], maxs[8] = np.float32(1e-42), np.float32(3e-42)  # denormals are kept
+    path = str(workdir / "uni_edge.bin")
+    membfile_py.write_uniform(path, words, mins, maxs, values, 255)
+    reader, want = abi.open_checked(path), oracle.open(path)
+    assert bits_equal(reader.lookup_words(words), want.batch_embedding(words))
+
+
+@pytest.mark.parametrize("dim", [3, 300])
+def test_full_parity(abi, oracle, synthetic, dim):
+    syn = synthetic("full", 8, rows=2000, dim=dim)
+    reader, want = abi.open_checked(syn.path), oracle.open(syn.path)
+    rng = np.random.default_rng(1)
+    words = queries_for(syn, rng, 1500)
+    got = reader.lookup_words(words)
+    assert bits_equal(got, want.batch_embedding(words))
+    assert bits_equal(reader.decode_range(0, 2000), syn.matrix[np.argsort([w.encode() for w in syn.words])])
+
+
+# ---- word -> row id ----
+def test_resolve_semantics(abi, oracle, workdir):
+    """strcmp semantics: cut at NUL, prefix / extension of keys, non-ASCII byte order,
+    empty string as a key, word beyond the last key."""
+    words = ["", "a", "ab", "abc", "b", "th", "the", "tho", "z", "zz", "é", "éa", "ж", "\U0001f600",
+             "x" * 300]
+    rng = np.random.default_rng(0)
+    matrix = rng.standard_normal((len(words), 8)).astype(np.float32)
+    path = str(workdir / "resolve.bin")
+    helpers.build_file(path, "full", 8, words, matrix)
+    reader, want = abi.open_checked(path), oracle.open(path)
+    assert reader.keys() == sorted(w.encode("utf-8") for w in words)
+    queries = words + ["t", "thee", "zzz", "ab\0c", "\0", "abd", "è", "\xff", "x" * 299, "x" * 301, b"\xc3",
+                       b"\xff\xfe"]
+    ids = reader.resolve(queries)
+    assert np.array_equal(ids, want.resolve(queries))
+    assert ids[queries.index("ab\0c")] == reader.keys().index(b"ab")
+    assert ids[queries.index("\0")] == 0 and ids[queries.index("zzz")] == -1
+    assert bits_equal(reader.lookup_words(queries), want.batch_embedding(queries))
+
+
+def test_resolve_large_vocabulary(abi, oracle, synthetic):
+    syn = synthetic("full", 8, rows=60000, dim=4, seed=9)
+    reader, want = abi.open_checked(syn.path), oracle.open(syn.path)
+    rng = np.random.default_rng(3)
+    ids = reader.resolve(syn.words)
+    order = np.argsort(np.array([w.encode() for w in syn.words], dtype=object))
+    expect = np.empty(len(order), np.int32)
+    expect[order] = np.arange(len(order))
+    assert np.array_equal(ids, expect)
+    queries = queries_for(syn, rng, 20000, 0.2)
+    assert np.array_equal(reader.resolve(queries), want.resolve(queries))
+
+
+# ---- ReadersUnion fused merges ----
+def union_case(synthetic):
+    a = synthetic("trained", 4, rows=3000, dim=300, seed=21)
+    b = synthetic("trained", 6, rows=2500, dim=300, seed=22)
+    c = synthetic("uniform", 8, rows=2000, dim=300, seed=23)
+    d = synthetic("full", 8, rows=1500, dim=300, seed=24)
+    return [a, b, c, d]
+
+
+@pytest.mark.parametrize("count", [2, 3, 4])
+def test_union_average_and_concatenate(abi, oracle, synthetic, count):
+    syns = union_case(synthetic)[:count]
+    readers = [abi.open_checked(s.path) for s in syns]
+    oracles = [oracle.open(s.path) for s in syns]
+    rng = np.random.default_rng(count)
+    words = []
+    for s in syns:
+        words += queries_for(s, rng, 700)
+    rng.shuffle(words)
+    parts = [o.batch_embedding(words) for o in oracles]
+    # the reference's own merge expressions (python/memb/readers_union.py:18,32)
+    want_avg = np.mean(parts, axis=0)
+    want_cat = np.concatenate(parts, axis=-1)
+    got_avg = helpers.union_lookup_words(abi, readers, abi.AVERAGE, words, 300)
+    got_cat = helpers.union_lookup_words(abi, readers, abi.CONCATENATE, words, 300 * count)
+    assert want_avg.dtype == np.float32 and bits_equal(got_avg, want_avg)
+    assert bits_equal(got_cat, want_cat)
+    ids = np.stack([o.resolve(words) for o in oracles])
+    assert bits_equal(helpers.union_decode_ids(abi, readers, abi.AVERAGE, ids, 300), want_avg)
+    assert bits_equal(helpers.union_decode_ids(abi, readers, abi.CONCATENATE, ids, 300 * count), want_cat)
+
+
+def test_union_mixed_dims_concatenate(abi, oracle, synthetic):
+    syns = [synthetic("trained", 5, rows=900, dim=100, seed=31), synthetic("uniform", 4, rows=800, dim=33, seed=32),
+            synthetic("trained", 3, rows=700, dim=7, seed=33)]
+    readers = [abi.open_checked(s.path) for s in syns]
+    rng = np.random.default_rng(8)
+    words = sum([queries_for(s, rng, 300) for s in syns], [])
+    want = np.concatenate([oracle.open(s.path).batch_embedding(words) for s in syns], axis=-1)
+    assert bits_equal(helpers.union_lookup_words(abi, readers, abi.CONCATENATE, words, 140), want)
+    status = abi.lib.memb_b200_union_lookup_words((helpers.c_void_p * 3)(*[r.h for r in readers]), 3, abi.AVERAGE,
+                                                  b"", None, 0, None)
+    assert status == abi.ERR_ARGUMENT  # dims differ (readers_union.py:7-10)
+
+
+# ---- the Python drop-in API on top ----
+def test_python_api(oracle, synthetic):
+    import memb_b200
+    from memb import Reader, ReadersUnion  # drop-in alias package
+
+    syn = synthetic("trained", 4, rows=3000, dim=300, seed=21)
+    other = synthetic("trained", 6, rows=2500, dim=300, seed=22)
+    want, want2 = oracle.open(syn.path), oracle.open(other.path)
+    reader = Reader(syn.path)
+    assert reader.dim == 300
+    assert reader.keys() == [k.decode() for k in want.keys()]
+    word = syn.words[5]
+    assert reader[word].shape == (300,) and bits_equal(reader[word], want.word_embedding(word))
+    assert np.all(reader["definitely missing"] == 0)
+    words = syn.words[:50] + ["nope", ""]
+    assert bits_equal(reader[words], want.batch_embedding(words))
+    with pytest.raises(TypeError):
+        reader[0]
+
+    class Tok:
+        word_index = {w: i + 1 for i, w in enumerate(syn.words[:40])}
+        num_words = 30
+
+    emb = reader.tokenizer_embedding(Tok)
+    assert emb.shape == (30, 300) and np.all(emb[0] == 0)
+    assert bits_equal(emb[1:], want.batch_embedding(syn.words[:29]))
+    assert bits_equal(reader._all_rows(None), want.decode_range(0, 3000))
+
+    union = ReadersUnion([reader, Reader(other.path)], "average")
+    parts = [want.batch_embedding(words), want2.batch_embedding(words)]
+    assert bits_equal(union[words], np.mean(parts, axis=0))
+    assert bits_equal(union[word], np.mean([p[5] for p in parts], axis=0))
+    cat = ReadersUnion([reader, Reader(other.path)], "concatenate")
+    assert cat.dim == 600 and bits_equal(cat[words], np.concatenate(parts, axis=-1))
+    assert union.keys() == sorted(set(syn.words) | set(other.words))
+    assert memb_b200._memb.launch_count() > 0
