@@ -198,7 +198,7 @@ std::vector<uint32_t> buildLut(const PrefixCodeTable& code, uint32_t lutBits)
     std::vector<uint32_t> lut(size_t(1) << lutBits, 0x8000u);
     for (size_t i = 0; i < code.keys.size(); ++i) {
         const uint32_t len = code.lengths[i];
-        const uint32_t entry = (static_cast<uint32_t>(code.keys[i]) << 18) | len;
+        const uint32_t entry = (static_cast<uint32_t>(code.keys[i]) << 16) | len;
         if (len <= lutBits) {
             const uint32_t first = static_cast<uint32_t>(code.codes[i]) << (lutBits - len);
             const uint32_t count = 1u << (lutBits - len);
@@ -340,12 +340,14 @@ void loadTrained(memb_b200_reader& r)
     p.lutShift = (replicas == 32 ? 25 : 30) - lutBits;
     p.lutMask = ((1u << lutBits) - 1) << (replicas == 32 ? 7 : 2);
     p.codebookSize = static_cast<uint32_t>(f.centroids.size());
-    p.slotBytes = ((maxRowBytes + 15) / 16) * 16 + 16;
+    p.rowWords = ((maxRowBytes + 15) / 16) * 4 + 4;
     r.trainedEscape = maxLen > lutBits;
-    r.trainedG = maxLen <= 8 ? 8 : 4;
+    // symbols per window reload: G * maxLen <= 64 bits
+    const uint32_t allowed = 64 / std::max(maxLen, 1u);
+    r.trainedG = allowed >= 16 ? 16 : allowed >= 8 ? 8 : allowed >= 7 ? 7 : allowed >= 5 ? 5 : 4;
 
-    const size_t fixedBytes = K::trainedLutBytes(lutBits, replicas) + K::trainedCodebookBytes(p.codebookSize);
-    const size_t perWarp = K::trainedWarpBytes(p.slotBytes);
+    const size_t fixedBytes = K::TRAINED_CODEBOOK_BYTES + K::trainedLutBytes(lutBits, replicas);
+    const size_t perWarp = K::trainedWarpBytes(p.rowWords);
     uint32_t warps = 0;
     if (r.smemOptin > fixedBytes) {
         warps = static_cast<uint32_t>(std::min<size_t>(K::TRAINED_MAX_WARPS, (r.smemOptin - fixedBytes) / perWarp));
@@ -354,7 +356,7 @@ void loadTrained(memb_b200_reader& r)
     if (warpsOpt > 0) {
         warps = std::min<uint32_t>(warps, static_cast<uint32_t>(warpsOpt));
     }
-    if (f.dim > K::TRAINED_MAX_DIM || g_optGeneric.load()) {
+    if (f.dim > K::TRAINED_MAX_DIM || p.codebookSize > 256 || g_optGeneric.load()) {
         warps = 0;
     }
     r.trainedWarps = warps;
@@ -424,41 +426,45 @@ bool vec4Ok(uint32_t dim, const K::OutputSpec& o)
 }
 
 template <int G, bool VEC4, bool ESCAPE>
-void launchTrainedEpi(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
-                      const K::OutputSpec& o, int epi, cudaStream_t stream)
+void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
+                         const K::OutputSpec& o, int epi, cudaStream_t stream)
 {
     const K::TrainedParams& p = r.trained;
-    const size_t smemBytes = K::trainedLutBytes(p.lutBits, p.lutReplicas) + K::trainedCodebookBytes(p.codebookSize) +
-                             size_t(r.trainedWarps) * K::trainedWarpBytes(p.slotBytes);
+    const size_t smemBytes = K::TRAINED_CODEBOOK_BYTES + K::trainedLutBytes(p.lutBits, p.lutReplicas) +
+                             size_t(r.trainedWarps) * K::trainedWarpBytes(p.rowWords);
     const uint64_t tiles = (n + 31) / 32;
     const unsigned grid = static_cast<unsigned>(
         std::min<uint64_t>(static_cast<uint64_t>(r.numSMs), (tiles + r.trainedWarps - 1) / r.trainedWarps));
     const unsigned block = r.trainedWarps * 32;
-    auto launch = [&](auto kernel) {
-        CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemBytes)));
-        kernel<<<grid, block, smemBytes, stream>>>(p, ids, rowBegin, n, o);
-    };
-    switch (epi) {
-    case K::EPI_WRITE:
-        launch(K::trained_decode_kernel<G, VEC4, ESCAPE, K::EPI_WRITE>);
-        break;
-    case K::EPI_ACCUMULATE:
-        launch(K::trained_decode_kernel<G, VEC4, ESCAPE, K::EPI_ACCUMULATE>);
-        break;
-    default:
-        launch(K::trained_decode_kernel<G, VEC4, ESCAPE, K::EPI_FINALIZE>);
-        break;
-    }
+    auto kernel = K::trained_decode_kernel<G, VEC4, ESCAPE>;
+    CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemBytes)));
+    kernel<<<grid, block, smemBytes, stream>>>(p, ids, rowBegin, n, o, epi);
 }
 
-template <int G, bool VEC4>
-void launchTrainedEsc(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
-                      const K::OutputSpec& o, int epi, cudaStream_t stream)
+template <bool VEC4>
+void launchTrainedG(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
+                    const K::OutputSpec& o, int epi, cudaStream_t stream)
 {
     if (r.trainedEscape) {
-        launchTrainedEpi<G, VEC4, true>(r, ids, rowBegin, n, o, epi, stream);
-    } else {
-        launchTrainedEpi<G, VEC4, false>(r, ids, rowBegin, n, o, epi, stream);
+        launchTrainedKernel<4, VEC4, true>(r, ids, rowBegin, n, o, epi, stream);
+        return;
+    }
+    switch (r.trainedG) {
+    case 16:
+        launchTrainedKernel<16, VEC4, false>(r, ids, rowBegin, n, o, epi, stream);
+        break;
+    case 8:
+        launchTrainedKernel<8, VEC4, false>(r, ids, rowBegin, n, o, epi, stream);
+        break;
+    case 7:
+        launchTrainedKernel<7, VEC4, false>(r, ids, rowBegin, n, o, epi, stream);
+        break;
+    case 5:
+        launchTrainedKernel<5, VEC4, false>(r, ids, rowBegin, n, o, epi, stream);
+        break;
+    default:
+        launchTrainedKernel<4, VEC4, false>(r, ids, rowBegin, n, o, epi, stream);
+        break;
     }
 }
 
@@ -485,12 +491,10 @@ void launchDecode(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBeg
             } else {
                 K::trained_decode_generic_kernel<K::EPI_FINALIZE><<<grid, 128, 0, stream>>>(r.trained, ids, rowBegin, n, o);
             }
-        } else if (r.trainedG == 8) {
-            vec ? launchTrainedEsc<8, true>(r, ids, rowBegin, n, o, epi, stream)
-                : launchTrainedEsc<8, false>(r, ids, rowBegin, n, o, epi, stream);
+        } else if (vec) {
+            launchTrainedG<true>(r, ids, rowBegin, n, o, epi, stream);
         } else {
-            vec ? launchTrainedEsc<4, true>(r, ids, rowBegin, n, o, epi, stream)
-                : launchTrainedEsc<4, false>(r, ids, rowBegin, n, o, epi, stream);
+            launchTrainedG<false>(r, ids, rowBegin, n, o, epi, stream);
         }
         break;
     case STORAGE_UNIFORM: {

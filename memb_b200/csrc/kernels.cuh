@@ -243,17 +243,29 @@ __global__ void pad_rows16_kernel(const uint32_t* __restrict__ rowBytes, uint32_
 // HBM layout (built once at load):
 //   blob      rows in row-id order, each padded to 16 B, 32-bit words byte-swapped
 //   rowOff16  rows+1 offsets into blob in 16 B units
-//   lut       2^lutBits entries, entry = (sym*4) << 16 | escape << 15 | len
-//             optionally replicated 32x in shared memory so lane l only ever
-//             touches bank l
+//   lut       2^lutBits entries, entry = sym << 16 | escape << 15 | len
 //   codebook  centroids, fp32
 //
 // Work decomposition: one warp owns a tile of 32 consecutive OUTPUT rows; lane l
 // decodes row l of the tile serially (rows are independent byte-aligned streams,
-// SURVEY D1), all lanes in lock step on the symbol index.  Compressed rows are
-// staged into shared memory with one cp.async.bulk per row completing on a
-// per-warp mbarrier; decoded values go through a swizzled 32x32 fp32 transpose
-// tile so that every global store instruction writes 4 x 128 contiguous bytes.
+// SURVEY D1), all lanes in lock step on the symbol index.
+//
+// Shared memory is the scarce resource of this kernel (ncu r01: 73 % of the LSU
+// shared-memory wavefront rate, half of it bank conflicts), so every structure
+// is laid out so that lane l only ever touches bank l:
+//   codebook  [0, 1 KiB)            fp32 centroids
+//   lut       [1 KiB, ...)          entry i of replica l at i*128 + l*4 (32 replicas),
+//                                   or one plain copy when the code is too long
+//   per warp  rows[w][l]            word w of lane l's compressed row at (w*32+l)*4
+//             tile[r]               ring of the last 128 decoded SYMBOLS of row r, 132 B stride
+// Compressed rows reach shared memory through registers: each lane pulls its own
+// row with 128-bit loads (four in flight) and scatters the words down its bank.
+// The decode loop keeps a 64-bit MSB-first window in two registers, re-centred
+// from shared memory every G symbols (G*maxLen <= 64), looks a symbol up with
+// one conflict-free LDS and packs four symbols into one word of the tile.  The
+// fp32 gather from the codebook happens on the way OUT of the transpose tile, so
+// the serial per-symbol chain carries no float and every global store is a
+// 128-bit streaming store covering 128 contiguous bytes per 8 lanes.
 struct TrainedParams {
     const uint4* blob;
     const uint32_t* rowOff16;
@@ -267,42 +279,23 @@ struct TrainedParams {
     uint32_t lutShift;      // window -> byte offset:  (hi >> lutShift) & lutMask
     uint32_t lutMask;
     uint32_t codebookSize;
-    uint32_t slotBytes;     // shared-memory bytes reserved per staged row (multiple of 16)
+    uint32_t rowWords;      // words reserved per staged row (max row units * 4 + 4)
 };
 
-__device__ __forceinline__ uint32_t smemAddr(const void* p)
+constexpr uint32_t TRAINED_CODEBOOK_BYTES = 1024;  // 256 centroids
+constexpr uint32_t TRAINED_CHUNK = 64;             // symbols decoded between two flushes
+constexpr uint32_t TRAINED_TILE_STRIDE = 132;      // bytes per tile row: ring of two chunks + 4 (bank skew)
+constexpr uint32_t TRAINED_TILE_BYTES = 32 * TRAINED_TILE_STRIDE;
+constexpr uint32_t TRAINED_MAX_DIM = 4095;  // consumed bits live in 16 bits: dim * 16 < 65536
+constexpr uint32_t TRAINED_MAX_WARPS = 24;  // 768 threads: up to 85 registers each
+
+__host__ __device__ inline uint32_t trainedLutBytes(uint32_t lutBits, uint32_t replicas)
 {
-    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+    return (4u << lutBits) * replicas;
 }
-__device__ __forceinline__ void mbarInit(uint32_t bar, uint32_t count)
+__host__ __device__ inline uint32_t trainedWarpBytes(uint32_t rowWords)
 {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbarExpectTx(uint32_t bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "MEMB_WAIT:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra MEMB_DONE;\n"
-        "bra MEMB_WAIT;\n"
-        "MEMB_DONE:\n"
-        "}\n" ::"r"(bar),
-        "r"(parity)
-        : "memory");
-}
-// 1-D bulk async copy global -> shared (TMA engine, SASS UBLKCP); src, dst and
-// bytes are multiples of 16.
-__device__ __forceinline__ void bulkCopyG2S(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar)
-{
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                 "l"(src), "r"(bytes), "r"(bar)
-                 : "memory");
+    return rowWords * 128 + TRAINED_TILE_BYTES;
 }
 
 struct BitWindow {
@@ -316,44 +309,40 @@ __device__ __noinline__ uint32_t escapeDecode(const CanonicalCode* __restrict__ 
     for (uint32_t l = code->minLen; l <= code->maxLen; ++l) {
         const uint32_t rel = (l ? (window >> (32 - l)) : 0u) - code->firstCode[l];
         if (rel < code->count[l]) {
-            return (static_cast<uint32_t>(code->keys[code->firstIndex[l] + rel]) << 18) | l;
+            return (static_cast<uint32_t>(code->keys[code->firstIndex[l] + rel]) << 16) | l;
         }
     }
     return 0;
 }
 
+// One symbol: LUT entry for the top bits of the window, window advanced by the
+// code length.  Returns the entry (symbol in bits 16..23).
 template <bool ESCAPE>
-__device__ __forceinline__ float decodeSymbol(BitWindow& w, const unsigned char* lutLane, uint32_t lutShift,
-                                              uint32_t lutMask, const unsigned char* codebook,
-                                              const CanonicalCode* __restrict__ code)
+__device__ __forceinline__ uint32_t decodeSymbol(BitWindow& w, const unsigned char* lutBase, uint32_t laneOr,
+                                                 uint32_t lutShift, uint32_t lutMask,
+                                                 const CanonicalCode* __restrict__ code)
 {
-    uint32_t e = *reinterpret_cast<const uint32_t*>(lutLane + ((w.hi >> lutShift) & lutMask));
+    // (idx << 7) | lane*4 in one LOP3; the base is uniform so the load is LDS [R + UR + imm]
+    uint32_t e = *reinterpret_cast<const uint32_t*>(lutBase + (((w.hi >> lutShift) & lutMask) | laneOr));
     if (ESCAPE) {
         if (e & 0x8000u) {
             e = escapeDecode(code, w.hi);
         }
     }
-    const float v = *reinterpret_cast<const float*>(codebook + (e >> 16));
     w.hi = __funnelshift_l(w.lo, w.hi, e);  // shift = e & 31 = code length
-    w.lo = __funnelshift_l(0u, w.lo, e);
+    w.lo = w.lo << (e & 31);
     w.consumed += e;
-    return v;
+    return e;
 }
 
-// Re-centre the 64-bit window on the row's current bit position: three aligned
-// 32-bit loads and two funnel shifts, no data-dependent branch.
-__device__ __forceinline__ void reloadWindow(BitWindow& w, const unsigned char* rowBase)
+// Re-centre the 64-bit window on the row's current bit position: three loads
+// down the lane's own bank and two funnel shifts, no data-dependent branch.
+__device__ __forceinline__ void reloadWindow(BitWindow& w, const unsigned char* rowLane)
 {
-    const uint32_t* p = reinterpret_cast<const uint32_t*>(rowBase + ((w.consumed >> 3) & 0x1ffcu));
-    const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(rowLane + ((w.consumed << 2) & 0x3ff80u));
+    const uint32_t w0 = p[0], w1 = p[32], w2 = p[64];
     w.hi = __funnelshift_l(w1, w0, w.consumed);
     w.lo = __funnelshift_l(w2, w1, w.consumed);
-}
-
-// Float4 slot of (row, quad) in the swizzled 32x32 fp32 tile.
-__device__ __forceinline__ float4* tileQuad(unsigned char* tile, uint32_t row, uint32_t quad)
-{
-    return reinterpret_cast<float4*>(tile + row * 128 + ((quad ^ (row & 7)) << 4));
 }
 
 __device__ __forceinline__ float applyEpilogue(float v, float old, int epi, float divisor)
@@ -365,45 +354,35 @@ __device__ __forceinline__ float applyEpilogue(float v, float old, int epi, floa
     return epi == EPI_ACCUMULATE ? s : __fdiv_rn(s, divisor);
 }
 
-constexpr uint32_t TRAINED_TILE_BYTES = 32 * 32 * 4;
-constexpr uint32_t TRAINED_MAX_DIM = 4095;  // consumed bits live in 16 bits: dim * 16 < 65536
-constexpr uint32_t TRAINED_MAX_WARPS = 24;
-
-__host__ __device__ inline uint32_t trainedLutBytes(uint32_t lutBits, uint32_t replicas)
+__device__ __forceinline__ uint4 loadRowUnit(const uint4* p)
 {
-    return (4u << lutBits) * replicas;
-}
-__host__ __device__ inline uint32_t trainedCodebookBytes(uint32_t codebookSize)
-{
-    return (codebookSize * 4 + 127) & ~127u;
-}
-__host__ __device__ inline uint32_t trainedWarpBytes(uint32_t slotBytes)
-{
-    return WARP * slotBytes + TRAINED_TILE_BYTES + 128;
+    uint4 v;
+    asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
 }
 
-// G = symbols decoded per window reload (4 for codes up to 16 bits, 8 for codes
-// up to 8 bits).  VEC4: dim, stride and column offset are multiples of 4 and the
-// output is 16 B aligned -> 128-bit shared loads and streaming 128-bit stores.
-template <int G, bool VEC4, bool ESCAPE, int EPI>
+// G = symbols decoded per window reload (G * maxLen <= 64).  VEC4: dim, stride
+// and column offset are multiples of 4 and the output is 16 B aligned -> 128-bit
+// streaming stores.  ESCAPE: some code is longer than the LUT is wide.
+template <int G, bool VEC4, bool ESCAPE>
 __global__ void __launch_bounds__(TRAINED_MAX_WARPS * WARP, 1)
 trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, uint32_t rowBegin, uint64_t n,
-                      const OutputSpec o)
+                      const OutputSpec o, const int epi)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     const uint32_t lane = threadIdx.x % WARP;
     const uint32_t warp = threadIdx.x / WARP;
     const uint32_t warpsPerCta = blockDim.x / WARP;
 
-    // shared layout: [lut][codebook][per warp: slots | tile | mbarrier]
     const uint32_t lutBytes = trainedLutBytes(p.lutBits, p.lutReplicas);
-    unsigned char* const codebook = smem + lutBytes;
-    unsigned char* const slots = codebook + trainedCodebookBytes(p.codebookSize) + warp * trainedWarpBytes(p.slotBytes);
-    unsigned char* const tile = slots + WARP * p.slotBytes;
-    const uint32_t bar = smemAddr(tile + TRAINED_TILE_BYTES);
+    float* const cbS = reinterpret_cast<float*>(smem);
+    unsigned char* const lutBase = smem + TRAINED_CODEBOOK_BYTES;
+    unsigned char* const warpBase = lutBase + lutBytes + warp * trainedWarpBytes(p.rowWords);
+    unsigned char* const rowLane = warpBase + lane * 4;          // word w of this lane's row at rowLane + w*128
+    unsigned char* const tile = warpBase + p.rowWords * 128;     // 32 rows x 132 B of symbols
 
     {
-        uint32_t* lutS = reinterpret_cast<uint32_t*>(smem);
+        uint32_t* lutS = reinterpret_cast<uint32_t*>(lutBase);
         const uint32_t entries = 1u << p.lutBits;
         if (p.lutReplicas == 1) {
             for (uint32_t i = threadIdx.x; i < entries; i += blockDim.x) {
@@ -414,151 +393,198 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                 lutS[i] = p.lut[i / WARP];
             }
         }
-        float* cbS = reinterpret_cast<float*>(codebook);
-        for (uint32_t i = threadIdx.x; i < p.codebookSize; i += blockDim.x) {
-            cbS[i] = p.codebook[i];
+        for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) {
+            cbS[i] = i < p.codebookSize ? p.codebook[i] : 0.f;
         }
-        if (lane == 0) {
-            mbarInit(bar, 1);
-        }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
 
-    const unsigned char* const lutLane = smem + (p.lutReplicas == 1 ? 0u : lane * 4u);
+    const uint32_t laneOr = p.lutReplicas == 1 ? 0u : lane * 4u;
     const uint32_t lutShift = p.lutShift, lutMask = p.lutMask;
     const uint64_t numTiles = (n + WARP - 1) / WARP;
     const uint64_t tileStride = static_cast<uint64_t>(gridDim.x) * warpsPerCta;
-    unsigned char* const mySlot = slots + lane * p.slotBytes;
     const uint32_t dim = p.dim;
-    uint32_t parity = 0;
+    const uint32_t fr = lane >> 4, fq = lane & 15;  // flush role: 16 lanes per output row, two rows per store
+    const uint64_t rowBytes = o.rowStride * 4;
 
-    // Stage the 32 rows of tile t; returns the lane's "row present" flag.
-    auto stage = [&](uint64_t t) -> bool {
+    // Where the lane's row of tile t lives.  A lane without a row (id < 0, id out
+    // of range, or past the end of the batch) decodes row 0 instead, which keeps it
+    // in lock step on valid data; its output is forced to zero at the flush.
+    auto locate = [&](uint64_t t, uint32_t& o16, uint32_t& units) -> bool {
         const uint64_t i = t * WARP + lane;
         int64_t row = -1;
-        if (i < n) {
-            row = ids ? static_cast<int64_t>(ids[i]) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
+        if (t < numTiles && i < n) {
+            row = ids ? static_cast<int64_t>(__ldg(ids + i)) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
         }
         const bool present = row >= 0 && row < static_cast<int64_t>(p.rows);
-        uint32_t o16 = 0, bytes = 0;
-        if (present) {
-            o16 = p.rowOff16[row];
-            bytes = (p.rowOff16[row + 1] - o16) * 16;
-        }
-        uint32_t total = bytes;
-#pragma unroll
-        for (int s = 16; s > 0; s >>= 1) {
-            total += __shfl_xor_sync(0xffffffffu, total, s);
-        }
-        if (lane == 0) {
-            mbarExpectTx(bar, total);
-        }
-        __syncwarp();
-        if (bytes) {
-            bulkCopyG2S(smemAddr(mySlot), p.blob + o16, bytes, bar);
+        o16 = 0;
+        units = 0;
+        if (p.rows) {
+            const uint32_t r = present ? static_cast<uint32_t>(row) : 0u;
+            o16 = __ldg(p.rowOff16 + r);
+            units = __ldg(p.rowOff16 + r + 1) - o16;
         }
         return present;
     };
 
     uint64_t t = static_cast<uint64_t>(blockIdx.x) * warpsPerCta + warp;
-    bool present = false;
-    if (t < numTiles) {
-        present = stage(t);
-    }
+    uint32_t o16 = 0, units = 0;
+    bool present = locate(t, o16, units);
+
     for (; t < numTiles; t += tileStride) {
         const uint32_t presentMask = __ballot_sync(0xffffffffu, present);
-        // lanes without a row decode a copy of some present row so that their
-        // bit position stays inside a staged slot; their output is forced to 0.
-        const uint32_t donor = presentMask ? (__ffs(presentMask) - 1) : lane;
-        const unsigned char* const rowBase = present ? mySlot : slots + donor * p.slotBytes;
-        mbarWait(bar, parity);
-        parity ^= 1;
+        // ---- stage: own row -> own bank, four 128-bit loads in flight ----
+        {
+            const uint4* src = p.blob + o16;
+            const uint32_t unitsMax = __reduce_max_sync(0xffffffffu, presentMask ? units : 0u);
+            for (uint32_t j = 0; j < unitsMax; j += 4) {
+                uint4 c[4];
+#pragma unroll
+                for (uint32_t k = 0; k < 4; ++k) {
+                    if (j + k < units) {
+                        c[k] = loadRowUnit(src + j + k);
+                    }
+                }
+#pragma unroll
+                for (uint32_t k = 0; k < 4; ++k) {
+                    if (j + k < units) {
+                        uint32_t* d = reinterpret_cast<uint32_t*>(rowLane + (j + k) * 512);
+                        d[0] = c[k].x;
+                        d[32] = c[k].y;
+                        d[64] = c[k].z;
+                        d[96] = c[k].w;
+                    }
+                }
+            }
+        }
+        // next tile's location is fetched under this tile's decode
+        uint32_t nextO16 = 0, nextUnits = 0;
+        const bool nextPresent = locate(t + tileStride, nextO16, nextUnits);
 
         BitWindow w;
         w.hi = w.lo = 0;
         w.consumed = 0;
         const uint64_t row0 = t * WARP;
         const uint32_t rowsHere = static_cast<uint32_t>(min(static_cast<uint64_t>(WARP), n - row0));
-        bool nextPresent = false;
+        uint32_t* const tileLane = reinterpret_cast<uint32_t*>(tile + lane * TRAINED_TILE_STRIDE);
+        unsigned char* const outTile = reinterpret_cast<unsigned char*>(o.out + row0 * o.rowStride + o.colOffset);
 
-        for (uint32_t c0 = 0; c0 < dim; c0 += 32) {
-            const uint32_t nsym = min(32u, dim - c0);
+        for (uint32_t c0 = 0; c0 < dim; c0 += TRAINED_CHUNK) {
+            const uint32_t nsym = min(TRAINED_CHUNK, dim - c0);
+            const uint32_t word0 = (c0 / 4) & 31u;  // ring position of this chunk's first word (0 or 16)
             if (presentMask) {
-                if (nsym == 32) {
+                if (nsym == TRAINED_CHUNK) {
 #pragma unroll
-                    for (int g = 0; g < 32 / G; ++g) {
-                        reloadWindow(w, rowBase);
+                    for (int q = 0; q < int(TRAINED_CHUNK / 4); ++q) {
+                        uint32_t acc = 0;
 #pragma unroll
-                        for (int h = 0; h < G / 4; ++h) {
-                            float4 v;
-                            v.x = decodeSymbol<ESCAPE>(w, lutLane, lutShift, lutMask, codebook, p.code);
-                            v.y = decodeSymbol<ESCAPE>(w, lutLane, lutShift, lutMask, codebook, p.code);
-                            v.z = decodeSymbol<ESCAPE>(w, lutLane, lutShift, lutMask, codebook, p.code);
-                            v.w = decodeSymbol<ESCAPE>(w, lutLane, lutShift, lutMask, codebook, p.code);
-                            *tileQuad(tile, lane, g * (G / 4) + h) = v;
+                        for (int k = 0; k < 4; ++k) {
+                            if ((q * 4 + k) % G == 0) {
+                                reloadWindow(w, rowLane);
+                            }
+                            const uint32_t e = decodeSymbol<ESCAPE>(w, lutBase, laneOr, lutShift, lutMask, p.code);
+                            // byte 2 of e (the symbol) -> byte k of acc
+                            acc = __byte_perm(acc, e, k == 0 ? 0x3216 : k == 1 ? 0x3260 : k == 2 ? 0x3610 : 0x6210);
                         }
+                        tileLane[word0 + q] = acc;
                     }
                 } else {
                     for (uint32_t s = 0; s < nsym; s += 4) {
-                        reloadWindow(w, rowBase);
-                        float v[4] = {0.f, 0.f, 0.f, 0.f};
+                        reloadWindow(w, rowLane);
+                        uint32_t acc = 0;
 #pragma unroll
                         for (uint32_t k = 0; k < 4; ++k) {
                             if (s + k < nsym) {
-                                v[k] = decodeSymbol<ESCAPE>(w, lutLane, lutShift, lutMask, codebook, p.code);
+                                const uint32_t e = decodeSymbol<ESCAPE>(w, lutBase, laneOr, lutShift, lutMask, p.code);
+                                acc |= ((e >> 16) & 0xffu) << (8 * k);
                             }
                         }
-                        *tileQuad(tile, lane, s / 4) = make_float4(v[0], v[1], v[2], v[3]);
+                        tileLane[word0 + s / 4] = acc;
                     }
                 }
             }
             __syncwarp();
-            // all compressed bytes of this tile are consumed once the last chunk
-            // is decoded: start staging the next tile under the final flush
-            if (c0 + 32 >= dim && t + tileStride < numTiles) {
-                nextPresent = stage(t + tileStride);
-            }
             if (VEC4) {
-                const uint32_t quads = nsym / 4;
-                const uint32_t q = lane & 7;
+                // Flush in whole 128 B lines of the OUTPUT: row r lags the decode by a_r
+                // 16 B units, where a_r is its start address modulo a line, so every
+                // store instruction writes two aligned 256 B runs (ncu/microbench r01:
+                // line-aligned runs of >= 256 B reach the plain-copy write rate, the
+                // unaligned 128 B pieces of the first version capped at 2.7 TB/s).
+                const bool last = c0 + TRAINED_CHUNK >= dim;
+                const int unitsBefore = int(c0 / 4);
+                const int unitsAfter = int((c0 + nsym) / 4);
+                if (!last && presentMask == 0xffffffffu && epi == EPI_WRITE) {
+                    // common case, straight-line: 16 x (1 word of symbols -> 4 centroids -> 128-bit store)
+                    unsigned char* rowPtr = outTile + fr * rowBytes;
+                    const uint32_t aBase = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(rowPtr) >> 4);
+                    const uint32_t aStep = static_cast<uint32_t>(rowBytes >> 3);  // two rows, in 16 B units
+                    const unsigned char* const tileRows = tile + fr * TRAINED_TILE_STRIDE;
 #pragma unroll
-                for (uint32_t it = 0; it < 8; ++it) {
-                    const uint32_t r = it * 4 + (lane >> 3);
-                    if (q < quads && r < rowsHere) {
-                        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if ((presentMask >> r) & 1u) {
-                            v = *tileQuad(tile, r, q);
+                    for (uint32_t it = 0; it < 16; ++it) {
+                        const int a = int((aBase + it * aStep) & 7u);
+                        const int j = unitsBefore - a + int(fq);
+                        const uint32_t s4 = *reinterpret_cast<const uint32_t*>(tileRows + it * 2 * TRAINED_TILE_STRIDE +
+                                                                               ((j & 31) << 2));
+                        float4 v;
+                        v.x = cbS[s4 & 0xffu];
+                        v.y = cbS[(s4 >> 8) & 0xffu];
+                        v.z = cbS[(s4 >> 16) & 0xffu];
+                        v.w = cbS[s4 >> 24];
+                        if (j >= 0) {
+                            __stcs(reinterpret_cast<float4*>(rowPtr) + j, v);
                         }
-                        float4* dst = reinterpret_cast<float4*>(o.out + (row0 + r) * o.rowStride + o.colOffset + c0) + q;
-                        if (EPI != EPI_WRITE) {
-                            const float4 old = *dst;
-                            v.x = applyEpilogue(v.x, old.x, EPI, o.divisor);
-                            v.y = applyEpilogue(v.y, old.y, EPI, o.divisor);
-                            v.z = applyEpilogue(v.z, old.z, EPI, o.divisor);
-                            v.w = applyEpilogue(v.w, old.w, EPI, o.divisor);
+                        rowPtr += 2 * rowBytes;
+                    }
+                } else
+                for (uint32_t it = 0; it < 16; ++it) {
+                    const uint32_t r = it * 2 + fr;
+                    if (r < rowsHere) {
+                        unsigned char* const rowPtr = outTile + r * rowBytes;
+                        const int a = int((reinterpret_cast<uintptr_t>(rowPtr) >> 4) & 7u);
+                        const int begin = max(unitsBefore - a, 0);
+                        const int end = last ? unitsAfter : unitsAfter - a;
+                        const bool rowPresent = (presentMask >> r) & 1u;
+                        const uint32_t* const tileRow = reinterpret_cast<const uint32_t*>(tile + r * TRAINED_TILE_STRIDE);
+                        for (int j = begin + int(fq); j < end; j += 16) {
+                            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (rowPresent) {
+                                const uint32_t s4 = tileRow[j & 31];
+                                v.x = cbS[s4 & 0xffu];
+                                v.y = cbS[(s4 >> 8) & 0xffu];
+                                v.z = cbS[(s4 >> 16) & 0xffu];
+                                v.w = cbS[s4 >> 24];
+                            }
+                            float4* dst = reinterpret_cast<float4*>(rowPtr) + j;
+                            if (epi != EPI_WRITE) {
+                                const float4 old = *dst;
+                                v.x = applyEpilogue(v.x, old.x, epi, o.divisor);
+                                v.y = applyEpilogue(v.y, old.y, epi, o.divisor);
+                                v.z = applyEpilogue(v.z, old.z, epi, o.divisor);
+                                v.w = applyEpilogue(v.w, old.w, epi, o.divisor);
+                            }
+                            __stcs(dst, v);
                         }
-                        __stcs(dst, v);
                     }
                 }
             } else {
                 for (uint32_t r = 0; r < rowsHere; ++r) {
-                    if (lane < nsym) {
-                        float v = 0.f;
-                        if ((presentMask >> r) & 1u) {
-                            v = reinterpret_cast<const float*>(tileQuad(tile, r, lane >> 2))[lane & 3];
+                    const bool rowPresent = (presentMask >> r) & 1u;
+                    const unsigned char* const tileRow = tile + r * TRAINED_TILE_STRIDE + word0 * 4;
+                    float* const dstRow = reinterpret_cast<float*>(outTile + r * rowBytes) + c0;
+                    for (uint32_t c = lane; c < nsym; c += WARP) {
+                        float v = rowPresent ? cbS[tileRow[c]] : 0.f;
+                        if (epi != EPI_WRITE) {
+                            v = applyEpilogue(v, dstRow[c], epi, o.divisor);
                         }
-                        float* dst = o.out + (row0 + r) * o.rowStride + o.colOffset + c0 + lane;
-                        if (EPI != EPI_WRITE) {
-                            v = applyEpilogue(v, *dst, EPI, o.divisor);
-                        }
-                        __stcs(dst, v);
+                        __stcs(dstRow + c, v);
                     }
                 }
             }
             __syncwarp();
         }
         present = nextPresent;
+        o16 = nextO16;
+        units = nextUnits;
     }
 }
 
