@@ -46,6 +46,7 @@ def parse_args():
     p.add_argument("--batch", type=int, default=1_000_000, help="row ids per step and per GPU")
     p.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (0 = auto)")
     p.add_argument("--no-extra", action="store_true", help="skip the secondary measurements")
+    p.add_argument("--trained-warps", type=int, default=0, help="experiment: cap resident warps per SM (0 = auto)")
     p.add_argument("--cache-dir", default=os.environ.get("MEMB_B200_BENCH_DIR", "/tmp/memb_b200_bench"))
     return p.parse_args()
 
@@ -293,6 +294,8 @@ def run_b200(args):
     build_s = build_table(args) if rank == 0 else 0.0
     barrier()
 
+    if args.trained_warps:
+        _memb.set_option("trained_warps", args.trained_warps)
     t0 = time.perf_counter()
     reader = memb_b200.Reader(table_path(args), device=local)
     open_s = time.perf_counter() - t0

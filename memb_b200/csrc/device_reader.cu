@@ -171,6 +171,10 @@ struct memb_b200_reader {
     std::vector<void*> owned;
 
     Scratch scratchIds, scratchOut, scratchQuery, scratchOffsets;
+    // dynamic tile scheduling of the trained kernel: one counter per launch in flight
+    static constexpr uint32_t TILE_COUNTERS = 256;
+    uint32_t* dTileCounters = nullptr;
+    std::atomic<uint32_t> launchSeq{0};
 
     ~memb_b200_reader()
     {
@@ -180,6 +184,7 @@ struct memb_b200_reader {
         if (dWords) cudaFree(dWords);
         if (dWordOffsets) cudaFree(dWordOffsets);
         if (dSlots) cudaFree(dSlots);
+        if (dTileCounters) cudaFree(dTileCounters);
         scratchIds.release();
         scratchOut.release();
         scratchQuery.release();
@@ -360,6 +365,7 @@ void loadTrained(memb_b200_reader& r)
         warps = 0;
     }
     r.trainedWarps = warps;
+    CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&r.dTileCounters), memb_b200_reader::TILE_COUNTERS * sizeof(uint32_t)));
 
     r.stats.max_code_len = maxLen;
     r.stats.lut_bits = lutBits;
@@ -436,9 +442,14 @@ void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t
     const unsigned grid = static_cast<unsigned>(
         std::min<uint64_t>(static_cast<uint64_t>(r.numSMs), (tiles + r.trainedWarps - 1) / r.trainedWarps));
     const unsigned block = r.trainedWarps * 32;
+    if (tiles + 4ull * grid * r.trainedWarps >= 0xffffffffull) {
+        fail(MEMB_B200_ERR_ARGUMENT, "decode: too many rows in one call");
+    }
     auto kernel = K::trained_decode_kernel<G, VEC4, ESCAPE>;
     CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemBytes)));
-    kernel<<<grid, block, smemBytes, stream>>>(p, ids, rowBegin, n, o, epi);
+    uint32_t* counter = r.dTileCounters + (const_cast<memb_b200_reader&>(r).launchSeq++ % memb_b200_reader::TILE_COUNTERS);
+    CUDA_CHECK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), stream));
+    kernel<<<grid, block, smemBytes, stream>>>(p, ids, rowBegin, n, o, epi, counter);
 }
 
 template <bool VEC4>

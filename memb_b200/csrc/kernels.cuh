@@ -287,7 +287,9 @@ constexpr uint32_t TRAINED_CHUNK = 64;             // symbols decoded between tw
 constexpr uint32_t TRAINED_TILE_STRIDE = 132;      // bytes per tile row: ring of two chunks + 4 (bank skew)
 constexpr uint32_t TRAINED_TILE_BYTES = 32 * TRAINED_TILE_STRIDE;
 constexpr uint32_t TRAINED_MAX_DIM = 4095;  // consumed bits live in 16 bits: dim * 16 < 65536
-constexpr uint32_t TRAINED_MAX_WARPS = 24;  // 768 threads: up to 85 registers each
+constexpr uint32_t TRAINED_MAX_WARPS = 12;  // three warps per scheduler ...
+constexpr uint32_t TRAINED_MAX_REGS = 168;  // ... each scheduler owns 16384 registers: 3 x 32 x 168 = 16128
+constexpr uint32_t TRAINED_PREFETCH_UNITS = 12;  // 192 B of the next row per lane held in registers
 
 __host__ __device__ inline uint32_t trainedLutBytes(uint32_t lutBits, uint32_t replicas)
 {
@@ -298,10 +300,10 @@ __host__ __device__ inline uint32_t trainedWarpBytes(uint32_t rowWords)
     return rowWords * 128 + TRAINED_TILE_BYTES;
 }
 
-struct BitWindow {
-    uint32_t hi, lo;    // 64 valid bits, MSB first
-    uint32_t consumed;  // low 16 bits: bits consumed in this row so far (junk above)
-};
+__device__ __forceinline__ uint32_t smemAddr(const void* p)
+{
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
 
 // Slow path for a window whose code is longer than the LUT width.
 __device__ __noinline__ uint32_t escapeDecode(const CanonicalCode* __restrict__ code, uint32_t window)
@@ -315,34 +317,115 @@ __device__ __noinline__ uint32_t escapeDecode(const CanonicalCode* __restrict__ 
     return 0;
 }
 
-// One symbol: LUT entry for the top bits of the window, window advanced by the
-// code length.  Returns the entry (symbol in bits 16..23).
-template <bool ESCAPE>
-__device__ __forceinline__ uint32_t decodeSymbol(BitWindow& w, const unsigned char* lutBase, uint32_t laneOr,
-                                                 uint32_t lutShift, uint32_t lutMask,
-                                                 const CanonicalCode* __restrict__ code)
+// ---- shared-memory accessors on 32-bit shared-window addresses ----
+// All hot-loop traffic goes through these instead of generic pointers: with
+// generic pointers nvcc re-derives the shared window base (S2UR SR_CgaCtaId /
+// ULEA) and adds it to every gather address; with explicit shared addresses the
+// loads compile to LDS [R + imm].  `volatile` keeps them ordered with respect to
+// each other and to __syncwarp; ptxas still schedules them for latency.
+__device__ __forceinline__ uint32_t ldsU32(uint32_t addr)
 {
-    // (idx << 7) | lane*4 in one LOP3; the base is uniform so the load is LDS [R + UR + imm]
-    uint32_t e = *reinterpret_cast<const uint32_t*>(lutBase + (((w.hi >> lutShift) & lutMask) | laneOr));
-    if (ESCAPE) {
-        if (e & 0x8000u) {
-            e = escapeDecode(code, w.hi);
-        }
-    }
-    w.hi = __funnelshift_l(w.lo, w.hi, e);  // shift = e & 31 = code length
-    w.lo = w.lo << (e & 31);
-    w.consumed += e;
-    return e;
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
 }
+template <int OFFSET>
+__device__ __forceinline__ uint32_t ldsU32At(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(OFFSET));
+    return v;
+}
+__device__ __forceinline__ float ldsF32(uint32_t addr)
+{
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void stsU32(uint32_t addr, uint32_t v)
+{
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v));
+}
+// 128-bit streaming store, executed only when `pred` (no branch).
+__device__ __forceinline__ void stcsF4If(bool pred, void* ptr, float4 v)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.u32 p, %5, 0;\n"
+        "@p st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};\n"
+        "}\n" ::"l"(ptr),
+        "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(static_cast<uint32_t>(pred))
+        : "memory");
+}
+
+// Four centroids for the four symbols packed in s4 (cb = shared address of the codebook).
+__device__ __forceinline__ float4 gatherCentroids(uint32_t cb, uint32_t s4)
+{
+    float4 v;
+    v.x = ldsF32(cb + ((s4 << 2) & 0x3fcu));
+    v.y = ldsF32(cb + ((s4 >> 6) & 0x3fcu));
+    v.z = ldsF32(cb + ((s4 >> 14) & 0x3fcu));
+    v.w = ldsF32(cb + ((s4 >> 22) & 0x3fcu));
+    return v;
+}
+
+// Decode state of one lane.  lut / rows are shared-window addresses.
+struct LaneDecoder {
+    uint32_t hi, lo;     // 64 valid bits of the row, MSB first
+    uint32_t consumed;   // low 16 bits: bits consumed in this row so far (junk above)
+    uint32_t lut;        // LUT base (+ nothing: the lane offset is OR-ed into the index)
+    uint32_t laneOr;     // lane * 4 when the LUT is replicated per bank, else 0
+    uint32_t lutShift, lutMask;
+    uint32_t rowLane;    // word w of this lane's compressed row lives at rowLane + w * 128
+};
 
 // Re-centre the 64-bit window on the row's current bit position: three loads
 // down the lane's own bank and two funnel shifts, no data-dependent branch.
-__device__ __forceinline__ void reloadWindow(BitWindow& w, const unsigned char* rowLane)
+__device__ __forceinline__ void reloadWindow(LaneDecoder& d)
 {
-    const uint32_t* p = reinterpret_cast<const uint32_t*>(rowLane + ((w.consumed << 2) & 0x3ff80u));
-    const uint32_t w0 = p[0], w1 = p[32], w2 = p[64];
-    w.hi = __funnelshift_l(w1, w0, w.consumed);
-    w.lo = __funnelshift_l(w2, w1, w.consumed);
+    const uint32_t a = d.rowLane + ((d.consumed << 2) & 0x3ff80u);
+    const uint32_t w0 = ldsU32At<0>(a), w1 = ldsU32At<128>(a), w2 = ldsU32At<256>(a);
+    d.hi = __funnelshift_l(w1, w0, d.consumed);
+    d.lo = __funnelshift_l(w2, w1, d.consumed);
+}
+
+// One symbol: LUT entry for the top bits of the window, window advanced by the
+// code length.  Returns the entry (symbol in bits 16..23).
+template <bool ESCAPE>
+__device__ __forceinline__ uint32_t decodeSymbol(LaneDecoder& d, const CanonicalCode* __restrict__ code)
+{
+    uint32_t e = ldsU32(d.lut + (((d.hi >> d.lutShift) & d.lutMask) | d.laneOr));
+    if (ESCAPE) {
+        if (e & 0x8000u) {
+            e = escapeDecode(code, d.hi);
+        }
+    }
+    d.hi = __funnelshift_l(d.lo, d.hi, e);  // shift = e & 31 = code length
+    d.lo = d.lo << (e & 31);
+    d.consumed += e;
+    return e;
+}
+
+// NW words of four symbols each, fully unrolled, window re-centred every G
+// symbols; word q goes to tileWord + 4*q.
+template <int NW, int G, bool ESCAPE>
+__device__ __forceinline__ void decodeWords(LaneDecoder& d, const CanonicalCode* __restrict__ code, uint32_t tileWord)
+{
+#pragma unroll
+    for (int q = 0; q < NW; ++q) {
+        uint32_t acc = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if ((q * 4 + k) % G == 0) {
+                reloadWindow(d);
+            }
+            const uint32_t e = decodeSymbol<ESCAPE>(d, code);
+            // byte 2 of e (the symbol) -> byte k of acc
+            acc = __byte_perm(acc, e, k == 0 ? 0x3216 : k == 1 ? 0x3260 : k == 2 ? 0x3610 : 0x6210);
+        }
+        stsU32(tileWord + 4 * q, acc);
+    }
 }
 
 __device__ __forceinline__ float applyEpilogue(float v, float old, int epi, float divisor)
@@ -365,9 +448,9 @@ __device__ __forceinline__ uint4 loadRowUnit(const uint4* p)
 // and column offset are multiples of 4 and the output is 16 B aligned -> 128-bit
 // streaming stores.  ESCAPE: some code is longer than the LUT is wide.
 template <int G, bool VEC4, bool ESCAPE>
-__global__ void __launch_bounds__(TRAINED_MAX_WARPS * WARP, 1)
+__global__ void __maxnreg__(TRAINED_MAX_REGS)
 trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, uint32_t rowBegin, uint64_t n,
-                      const OutputSpec o, const int epi)
+                      const OutputSpec o, const int epi, uint32_t* __restrict__ tileCounter)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     const uint32_t lane = threadIdx.x % WARP;
@@ -375,14 +458,9 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     const uint32_t warpsPerCta = blockDim.x / WARP;
 
     const uint32_t lutBytes = trainedLutBytes(p.lutBits, p.lutReplicas);
-    float* const cbS = reinterpret_cast<float*>(smem);
-    unsigned char* const lutBase = smem + TRAINED_CODEBOOK_BYTES;
-    unsigned char* const warpBase = lutBase + lutBytes + warp * trainedWarpBytes(p.rowWords);
-    unsigned char* const rowLane = warpBase + lane * 4;          // word w of this lane's row at rowLane + w*128
-    unsigned char* const tile = warpBase + p.rowWords * 128;     // 32 rows x 132 B of symbols
-
     {
-        uint32_t* lutS = reinterpret_cast<uint32_t*>(lutBase);
+        float* cbS = reinterpret_cast<float*>(smem);
+        uint32_t* lutS = reinterpret_cast<uint32_t*>(smem + TRAINED_CODEBOOK_BYTES);
         const uint32_t entries = 1u << p.lutBits;
         if (p.lutReplicas == 1) {
             for (uint32_t i = threadIdx.x; i < entries; i += blockDim.x) {
@@ -399,45 +477,107 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     }
     __syncthreads();
 
-    const uint32_t laneOr = p.lutReplicas == 1 ? 0u : lane * 4u;
-    const uint32_t lutShift = p.lutShift, lutMask = p.lutMask;
+    // shared-window addresses
+    const uint32_t cb = smemAddr(smem);
+    const uint32_t warpBase = cb + TRAINED_CODEBOOK_BYTES + lutBytes + warp * trainedWarpBytes(p.rowWords);
+    const uint32_t tile = warpBase + p.rowWords * 128;  // 32 rows x 132 B of symbols (ring of two chunks)
+    LaneDecoder d;
+    d.lut = cb + TRAINED_CODEBOOK_BYTES;
+    d.laneOr = p.lutReplicas == 1 ? 0u : lane * 4u;
+    d.lutShift = p.lutShift;
+    d.lutMask = p.lutMask;
+    d.rowLane = warpBase + lane * 4;
+    const uint32_t tileLane = tile + lane * TRAINED_TILE_STRIDE;
+
     const uint64_t numTiles = (n + WARP - 1) / WARP;
-    const uint64_t tileStride = static_cast<uint64_t>(gridDim.x) * warpsPerCta;
+    const uint32_t totalWarps = gridDim.x * warpsPerCta;
     const uint32_t dim = p.dim;
     const uint32_t fr = lane >> 4, fq = lane & 15;  // flush role: 16 lanes per output row, two rows per store
     const uint64_t rowBytes = o.rowStride * 4;
 
-    // Where the lane's row of tile t lives.  A lane without a row (id < 0, id out
-    // of range, or past the end of the batch) decodes row 0 instead, which keeps it
-    // in lock step on valid data; its output is forced to zero at the flush.
-    auto locate = [&](uint64_t t, uint32_t& o16, uint32_t& units) -> bool {
-        const uint64_t i = t * WARP + lane;
-        int64_t row = -1;
-        if (t < numTiles && i < n) {
-            row = ids ? static_cast<int64_t>(__ldg(ids + i)) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
+    // Three-stage software pipeline over the warp's tiles (every stage is one HBM
+    // round trip, none of them is waited for in the tile that issues it):
+    //   tile t+3  row id             (ids[i], or rowBegin + i for a range decode)
+    //   tile t+2  row offsets        (rowOff16[row], rowOff16[row + 1])
+    //   tile t+1  compressed row     (up to TRAINED_PREFETCH_UNITS x 16 B into registers)
+    //   tile t    decode from shared memory
+    // Tiles are handed out dynamically (one atomicAdd per tile, also a stage ahead)
+    // after a static first round, so no SM idles while another still has a queue.
+    // A lane without a row (id < 0, id out of range, past the end of the batch)
+    // decodes row 0 instead, which keeps it in lock step on valid data; its output
+    // is forced to zero at the flush.
+    // (the loaded id is only touched one tile later: nothing here consumes it)
+    auto fetchId = [&](uint64_t tt, bool& has) -> uint32_t {
+        const uint64_t i = tt * WARP + lane;
+        has = tt < numTiles && i < n;
+        if (!has) {
+            return 0;
         }
-        const bool present = row >= 0 && row < static_cast<int64_t>(p.rows);
-        o16 = 0;
-        units = 0;
+        return ids ? static_cast<uint32_t>(__ldg(ids + i)) : rowBegin + static_cast<uint32_t>(i);
+    };
+    auto fetchOffsets = [&](uint32_t row, bool has, uint32_t& lo, uint32_t& hi) -> bool {
+        const bool ok = has && row < p.rows;  // a negative id is a huge unsigned one
+        lo = hi = 0;
         if (p.rows) {
-            const uint32_t r = present ? static_cast<uint32_t>(row) : 0u;
-            o16 = __ldg(p.rowOff16 + r);
-            units = __ldg(p.rowOff16 + r + 1) - o16;
+            const uint32_t r = ok ? row : 0u;
+            lo = __ldg(p.rowOff16 + r);
+            hi = __ldg(p.rowOff16 + r + 1);
         }
-        return present;
+        return ok;
+    };
+    uint4 pre[TRAINED_PREFETCH_UNITS];
+    auto prefetchRows = [&](uint32_t rowO16, uint32_t rowUnits) {
+        const uint4* src = p.blob + rowO16;
+#pragma unroll
+        for (uint32_t k = 0; k < TRAINED_PREFETCH_UNITS; ++k) {
+            if (k < rowUnits) {
+                pre[k] = loadRowUnit(src + k);
+            }
+        }
     };
 
+    // tile queue of this warp: t (decoding), t1 (rows in flight), t2 (offsets in
+    // flight), t3 (id in flight); `ticket` is lane 0's pending atomicAdd result
     uint64_t t = static_cast<uint64_t>(blockIdx.x) * warpsPerCta + warp;
-    uint32_t o16 = 0, units = 0;
-    bool present = locate(t, o16, units);
+    uint64_t t1 = t + totalWarps, t2 = t1 + totalWarps, t3 = t2 + totalWarps;
+    uint32_t ticket = 0;
+    auto drawTicket = [&]() {
+        if (lane == 0) {
+            ticket = atomicAdd(tileCounter, 1u);
+        }
+    };
+    auto redeemTicket = [&]() -> uint64_t {
+        return 4ull * totalWarps + __shfl_sync(0xffffffffu, ticket, 0);
+    };
+    drawTicket();
+    uint32_t offLo, offHi, offLoNext, offHiNext;
+    bool hasRow;
+    uint32_t rowAfter = fetchId(t, hasRow);
+    bool present = fetchOffsets(rowAfter, hasRow, offLo, offHi);
+    rowAfter = fetchId(t1, hasRow);
+    bool presentNext = fetchOffsets(rowAfter, hasRow, offLoNext, offHiNext);
+    rowAfter = fetchId(t2, hasRow);
+    uint32_t o16 = offLo, units = offHi - offLo;
+    prefetchRows(o16, units);
 
-    for (; t < numTiles; t += tileStride) {
+    while (t < numTiles) {
         const uint32_t presentMask = __ballot_sync(0xffffffffu, present);
-        // ---- stage: own row -> own bank, four 128-bit loads in flight ----
+        // ---- stage: own row -> own bank ----
+#pragma unroll
+        for (uint32_t k = 0; k < TRAINED_PREFETCH_UNITS; ++k) {
+            if (k < units) {
+                const uint32_t a = d.rowLane + k * 512;
+                stsU32(a, pre[k].x);
+                stsU32(a + 128, pre[k].y);
+                stsU32(a + 256, pre[k].z);
+                stsU32(a + 384, pre[k].w);
+            }
+        }
         {
+            // rows longer than the prefetch window: the rest comes straight from HBM
             const uint4* src = p.blob + o16;
             const uint32_t unitsMax = __reduce_max_sync(0xffffffffu, presentMask ? units : 0u);
-            for (uint32_t j = 0; j < unitsMax; j += 4) {
+            for (uint32_t j = TRAINED_PREFETCH_UNITS; j < unitsMax; j += 4) {
                 uint4 c[4];
 #pragma unroll
                 for (uint32_t k = 0; k < 4; ++k) {
@@ -448,58 +588,64 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
 #pragma unroll
                 for (uint32_t k = 0; k < 4; ++k) {
                     if (j + k < units) {
-                        uint32_t* d = reinterpret_cast<uint32_t*>(rowLane + (j + k) * 512);
-                        d[0] = c[k].x;
-                        d[32] = c[k].y;
-                        d[64] = c[k].z;
-                        d[96] = c[k].w;
+                        const uint32_t a = d.rowLane + (j + k) * 512;
+                        stsU32(a, c[k].x);
+                        stsU32(a + 128, c[k].y);
+                        stsU32(a + 256, c[k].z);
+                        stsU32(a + 384, c[k].w);
                     }
                 }
             }
         }
-        // next tile's location is fetched under this tile's decode
-        uint32_t nextO16 = 0, nextUnits = 0;
-        const bool nextPresent = locate(t + tileStride, nextO16, nextUnits);
+        // advance the pipeline: rows of t+1, offsets of t+2, id of t+3
+        const uint32_t o16Next = offLoNext, unitsNext = offHiNext - offLoNext;
+        prefetchRows(o16Next, unitsNext);
+        uint32_t offLoAfter, offHiAfter;
+        const bool presentAfter = fetchOffsets(rowAfter, hasRow, offLoAfter, offHiAfter);
+        rowAfter = fetchId(t3, hasRow);
+        const uint64_t t4 = redeemTicket();
+        drawTicket();
 
-        BitWindow w;
-        w.hi = w.lo = 0;
-        w.consumed = 0;
+        d.hi = d.lo = 0;
+        d.consumed = 0;
         const uint64_t row0 = t * WARP;
         const uint32_t rowsHere = static_cast<uint32_t>(min(static_cast<uint64_t>(WARP), n - row0));
-        uint32_t* const tileLane = reinterpret_cast<uint32_t*>(tile + lane * TRAINED_TILE_STRIDE);
         unsigned char* const outTile = reinterpret_cast<unsigned char*>(o.out + row0 * o.rowStride + o.colOffset);
 
         for (uint32_t c0 = 0; c0 < dim; c0 += TRAINED_CHUNK) {
             const uint32_t nsym = min(TRAINED_CHUNK, dim - c0);
             const uint32_t word0 = (c0 / 4) & 31u;  // ring position of this chunk's first word (0 or 16)
             if (presentMask) {
+                uint32_t tw = tileLane + word0 * 4;
                 if (nsym == TRAINED_CHUNK) {
-#pragma unroll
-                    for (int q = 0; q < int(TRAINED_CHUNK / 4); ++q) {
-                        uint32_t acc = 0;
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            if ((q * 4 + k) % G == 0) {
-                                reloadWindow(w, rowLane);
-                            }
-                            const uint32_t e = decodeSymbol<ESCAPE>(w, lutBase, laneOr, lutShift, lutMask, p.code);
-                            // byte 2 of e (the symbol) -> byte k of acc
-                            acc = __byte_perm(acc, e, k == 0 ? 0x3216 : k == 1 ? 0x3260 : k == 2 ? 0x3610 : 0x6210);
-                        }
-                        tileLane[word0 + q] = acc;
-                    }
+                    decodeWords<TRAINED_CHUNK / 4, G, ESCAPE>(d, p.code, tw);
                 } else {
-                    for (uint32_t s = 0; s < nsym; s += 4) {
-                        reloadWindow(w, rowLane);
+                    uint32_t nw = nsym / 4;
+                    if (nw & 8) {
+                        decodeWords<8, G, ESCAPE>(d, p.code, tw);
+                        tw += 32;
+                    }
+                    if (nw & 4) {
+                        decodeWords<4, G, ESCAPE>(d, p.code, tw);
+                        tw += 16;
+                    }
+                    if (nw & 2) {
+                        decodeWords<2, G, ESCAPE>(d, p.code, tw);
+                        tw += 8;
+                    }
+                    if (nw & 1) {
+                        decodeWords<1, G, ESCAPE>(d, p.code, tw);
+                        tw += 4;
+                    }
+                    const uint32_t rest = nsym & 3;
+                    if (rest) {
+                        reloadWindow(d);
                         uint32_t acc = 0;
-#pragma unroll
-                        for (uint32_t k = 0; k < 4; ++k) {
-                            if (s + k < nsym) {
-                                const uint32_t e = decodeSymbol<ESCAPE>(w, lutBase, laneOr, lutShift, lutMask, p.code);
-                                acc |= ((e >> 16) & 0xffu) << (8 * k);
-                            }
+                        for (uint32_t k = 0; k < rest; ++k) {
+                            const uint32_t e = decodeSymbol<ESCAPE>(d, p.code);
+                            acc |= ((e >> 16) & 0xffu) << (8 * k);
                         }
-                        tileLane[word0 + s / 4] = acc;
+                        stsU32(tw, acc);
                     }
                 }
             }
@@ -507,72 +653,76 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
             if (VEC4) {
                 // Flush in whole 128 B lines of the OUTPUT: row r lags the decode by a_r
                 // 16 B units, where a_r is its start address modulo a line, so every
-                // store instruction writes two aligned 256 B runs (ncu/microbench r01:
+                // store instruction writes two aligned 256 B runs (microbench r01:
                 // line-aligned runs of >= 256 B reach the plain-copy write rate, the
                 // unaligned 128 B pieces of the first version capped at 2.7 TB/s).
                 const bool last = c0 + TRAINED_CHUNK >= dim;
                 const int unitsBefore = int(c0 / 4);
                 const int unitsAfter = int((c0 + nsym) / 4);
-                if (!last && presentMask == 0xffffffffu && epi == EPI_WRITE) {
-                    // common case, straight-line: 16 x (1 word of symbols -> 4 centroids -> 128-bit store)
-                    unsigned char* rowPtr = outTile + fr * rowBytes;
-                    const uint32_t aBase = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(rowPtr) >> 4);
-                    const uint32_t aStep = static_cast<uint32_t>(rowBytes >> 3);  // two rows, in 16 B units
-                    const unsigned char* const tileRows = tile + fr * TRAINED_TILE_STRIDE;
+                unsigned char* rowPtr = outTile + fr * rowBytes;
+                const uint32_t aBase = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(rowPtr) >> 4);
+                const uint32_t aStep = static_cast<uint32_t>(rowBytes >> 3);  // two rows, in 16 B units
+                const uint32_t tileRows = tile + fr * TRAINED_TILE_STRIDE;
+                if (presentMask == 0xffffffffu && epi == EPI_WRITE) {
+                    // common case, straight-line: 16 x (1 word of symbols -> 4 centroids -> 128-bit store);
+                    // the last chunk also drains the units the rows were lagging by (second pass)
 #pragma unroll
                     for (uint32_t it = 0; it < 16; ++it) {
                         const int a = int((aBase + it * aStep) & 7u);
                         const int j = unitsBefore - a + int(fq);
-                        const uint32_t s4 = *reinterpret_cast<const uint32_t*>(tileRows + it * 2 * TRAINED_TILE_STRIDE +
-                                                                               ((j & 31) << 2));
-                        float4 v;
-                        v.x = cbS[s4 & 0xffu];
-                        v.y = cbS[(s4 >> 8) & 0xffu];
-                        v.z = cbS[(s4 >> 16) & 0xffu];
-                        v.w = cbS[s4 >> 24];
-                        if (j >= 0) {
-                            __stcs(reinterpret_cast<float4*>(rowPtr) + j, v);
+                        const int end = last ? unitsAfter : unitsAfter - a;
+                        const uint32_t s4 = ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j & 31) << 2));
+                        const float4 v = gatherCentroids(cb, s4);
+                        stcsF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr + it * 2 * rowBytes) + j, v);
+                    }
+                    if (last) {
+#pragma unroll
+                        for (uint32_t it = 0; it < 16; ++it) {
+                            const int a = int((aBase + it * aStep) & 7u);
+                            const int j2 = unitsBefore - a + int(fq) + 16;
+                            const uint32_t t4 = ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j2 & 31) << 2));
+                            const float4 u = gatherCentroids(cb, t4);
+                            stcsF4If(j2 < unitsAfter, reinterpret_cast<float4*>(rowPtr + it * 2 * rowBytes) + j2, u);
+                        }
+                    }
+                } else {
+                    for (uint32_t it = 0; it < 16; ++it) {
+                        const uint32_t r = it * 2 + fr;
+                        if (r < rowsHere) {
+                            const int a = int((aBase + it * aStep) & 7u);
+                            const int begin = max(unitsBefore - a, 0);
+                            const int end = last ? unitsAfter : unitsAfter - a;
+                            const bool rowPresent = (presentMask >> r) & 1u;
+                            for (int j = begin + int(fq); j < end; j += 16) {
+                                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                                if (rowPresent) {
+                                    v = gatherCentroids(cb, ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j & 31) << 2)));
+                                }
+                                float4* dst = reinterpret_cast<float4*>(rowPtr) + j;
+                                if (epi != EPI_WRITE) {
+                                    const float4 old = *dst;
+                                    v.x = applyEpilogue(v.x, old.x, epi, o.divisor);
+                                    v.y = applyEpilogue(v.y, old.y, epi, o.divisor);
+                                    v.z = applyEpilogue(v.z, old.z, epi, o.divisor);
+                                    v.w = applyEpilogue(v.w, old.w, epi, o.divisor);
+                                }
+                                __stcs(dst, v);
+                            }
                         }
                         rowPtr += 2 * rowBytes;
-                    }
-                } else
-                for (uint32_t it = 0; it < 16; ++it) {
-                    const uint32_t r = it * 2 + fr;
-                    if (r < rowsHere) {
-                        unsigned char* const rowPtr = outTile + r * rowBytes;
-                        const int a = int((reinterpret_cast<uintptr_t>(rowPtr) >> 4) & 7u);
-                        const int begin = max(unitsBefore - a, 0);
-                        const int end = last ? unitsAfter : unitsAfter - a;
-                        const bool rowPresent = (presentMask >> r) & 1u;
-                        const uint32_t* const tileRow = reinterpret_cast<const uint32_t*>(tile + r * TRAINED_TILE_STRIDE);
-                        for (int j = begin + int(fq); j < end; j += 16) {
-                            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                            if (rowPresent) {
-                                const uint32_t s4 = tileRow[j & 31];
-                                v.x = cbS[s4 & 0xffu];
-                                v.y = cbS[(s4 >> 8) & 0xffu];
-                                v.z = cbS[(s4 >> 16) & 0xffu];
-                                v.w = cbS[s4 >> 24];
-                            }
-                            float4* dst = reinterpret_cast<float4*>(rowPtr) + j;
-                            if (epi != EPI_WRITE) {
-                                const float4 old = *dst;
-                                v.x = applyEpilogue(v.x, old.x, epi, o.divisor);
-                                v.y = applyEpilogue(v.y, old.y, epi, o.divisor);
-                                v.z = applyEpilogue(v.z, old.z, epi, o.divisor);
-                                v.w = applyEpilogue(v.w, old.w, epi, o.divisor);
-                            }
-                            __stcs(dst, v);
-                        }
                     }
                 }
             } else {
                 for (uint32_t r = 0; r < rowsHere; ++r) {
                     const bool rowPresent = (presentMask >> r) & 1u;
-                    const unsigned char* const tileRow = tile + r * TRAINED_TILE_STRIDE + word0 * 4;
+                    const uint32_t tileRow = tile + r * TRAINED_TILE_STRIDE + word0 * 4;
                     float* const dstRow = reinterpret_cast<float*>(outTile + r * rowBytes) + c0;
                     for (uint32_t c = lane; c < nsym; c += WARP) {
-                        float v = rowPresent ? cbS[tileRow[c]] : 0.f;
+                        float v = 0.f;
+                        if (rowPresent) {
+                            const uint32_t s4 = ldsU32(tileRow + (c & ~3u));
+                            v = ldsF32(cb + (((s4 >> (8 * (c & 3))) & 0xffu) << 2));
+                        }
                         if (epi != EPI_WRITE) {
                             v = applyEpilogue(v, dstRow[c], epi, o.divisor);
                         }
@@ -582,9 +732,16 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
             }
             __syncwarp();
         }
-        present = nextPresent;
-        o16 = nextO16;
-        units = nextUnits;
+        present = presentNext;
+        o16 = o16Next;
+        units = unitsNext;
+        presentNext = presentAfter;
+        offLoNext = offLoAfter;
+        offHiNext = offHiAfter;
+        t = t1;
+        t1 = t2;
+        t2 = t3;
+        t3 = t4;
     }
 }
 
