@@ -150,6 +150,7 @@ struct memb_b200_reader {
     int device = 0;
     int numSMs = 148;
     size_t smemOptin = 0;
+    uint32_t smemBase = 0;  // first dynamic shared byte of a kernel (shared-window address)
     std::unique_ptr<MembFile> file;
     memb_b200_load_stats stats{};
     cudaStream_t stream = nullptr;
@@ -195,23 +196,33 @@ struct memb_b200_reader {
 
 namespace {
 
-// Direct-table LUT over the top `lutBits` bits of the window
+// Direct-table LUT over the next `lutBits` bits of the stream
 // (the GPU analogue of the table built in src/huffman_table_decoder.h:44-56;
-// fuzz in SURVEY §0 shows any table width decodes identically).
-std::vector<uint32_t> buildLut(const PrefixCodeTable& code, uint32_t lutBits)
+// fuzz in SURVEY §0 shows any table width decodes identically).  The decode
+// kernel holds its window LSB-first, so entry i is the code whose first bit is
+// bit 0 of i: the canonical (MSB-first) prefix with its bits reversed.
+// entry = (key << symShift) << 16 | escape << 15 | length.
+std::vector<uint32_t> buildLut(const PrefixCodeTable& code, uint32_t lutBits, uint32_t symShift)
 {
+    const auto reversed = [lutBits](uint32_t prefix) {
+        uint32_t r = 0;
+        for (uint32_t b = 0; b < lutBits; ++b) {
+            r |= ((prefix >> b) & 1u) << (lutBits - 1 - b);
+        }
+        return r;
+    };
     std::vector<uint32_t> lut(size_t(1) << lutBits, 0x8000u);
     for (size_t i = 0; i < code.keys.size(); ++i) {
         const uint32_t len = code.lengths[i];
-        const uint32_t entry = (static_cast<uint32_t>(code.keys[i]) << 16) | len;
+        const uint32_t entry = ((static_cast<uint32_t>(code.keys[i]) << symShift) << 16) | len;
         if (len <= lutBits) {
             const uint32_t first = static_cast<uint32_t>(code.codes[i]) << (lutBits - len);
             const uint32_t count = 1u << (lutBits - len);
             for (uint32_t k = 0; k < count; ++k) {
-                lut[first + k] = entry;
+                lut[reversed(first + k)] = entry;
             }
         } else {
-            lut[code.codes[i] >> (len - lutBits)] = 0x8000u;  // escape: resolved bit-serially
+            lut[reversed(code.codes[i] >> (len - lutBits))] = 0x8000u;  // escape: resolved bit-serially
         }
     }
     return lut;
@@ -257,6 +268,21 @@ void buildVocabulary(memb_b200_reader& r)
     }
 }
 
+// First dynamic shared byte of a kernel without static shared memory on this device.
+uint32_t probeSmemBase(cudaStream_t stream)
+{
+    uint32_t* dBase = nullptr;
+    uint32_t base = 0;
+    CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&dBase), sizeof(uint32_t)));
+    K::smem_base_probe_kernel<<<1, 1, 1024, stream>>>(dBase);
+    ++g_launches;
+    CUDA_CHECK(cudaGetLastError());
+    CUDA_CHECK(cudaMemcpyAsync(&base, dBase, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+    CUDA_CHECK(cudaStreamSynchronize(stream));
+    CUDA_CHECK(cudaFree(dBase));
+    return base;
+}
+
 void loadTrained(memb_b200_reader& r)
 {
     MembFile& f = *r.file;
@@ -274,6 +300,24 @@ void loadTrained(memb_b200_reader& r)
     r.stats.upload_ms += msSince(t0);
 
     const auto t1 = std::chrono::steady_clock::now();
+    // decode tables first: the LUT flavour fixes how the rows are re-packed
+    const uint32_t maxLen = f.code.maxLen;
+    int64_t replicasOpt = g_optLutReplicas.load();
+    uint32_t replicas, lutBits, padBits;
+    if (replicasOpt == 32 || (replicasOpt == 0 && maxLen <= 9)) {
+        replicas = 32;  // one copy per shared-memory bank, entry i of lane l at i*128 + l*4
+        lutBits = std::max(1u, std::min(maxLen, 9u));
+        padBits = 7;
+    } else {
+        replicas = 1;
+        lutBits = std::max(1u, std::min(maxLen, 12u));
+        padBits = 2;
+    }
+    const bool escape = maxLen > lutBits;
+    const uint32_t codebookSize = static_cast<uint32_t>(f.centroids.size());
+    // <= 64 centroids: the symbol field carries sym * 4, the byte offset into the codebook
+    const uint32_t symShift = (!escape && codebookSize <= 64) ? 2u : 0u;
+
     // exact row lengths -> offsets of the 16 B-aligned re-pack
     uint32_t* dRowBytes = nullptr;
     CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&dRowBytes), std::max<size_t>(size_t(rows) * 4, 16)));
@@ -288,12 +332,14 @@ void loadTrained(memb_b200_reader& r)
     CUDA_CHECK(cudaStreamSynchronize(r.stream));
     std::vector<uint32_t> rowOff16(size_t(rows) + 1);
     uint64_t units = 0, payload = 0;
-    uint32_t maxRowBytes = 0;
+    uint32_t maxRowUnits = 0;
     for (uint32_t i = 0; i < rows; ++i) {
         rowOff16[i] = static_cast<uint32_t>(units);
-        units += (rowBytes[i] + 15) / 16;
+        // padBits (< 8) extra bits in front of the row: one more byte
+        const uint32_t rowUnits = rowBytes[i] ? (rowBytes[i] + 1 + 15) / 16 : 0;
+        units += rowUnits;
         payload += rowBytes[i];
-        maxRowBytes = std::max(maxRowBytes, rowBytes[i]);
+        maxRowUnits = std::max(maxRowUnits, rowUnits);
         if (units > 0xffffffffULL) {
             fail(MEMB_B200_ERR_FORMAT, "memb file: re-packed rows exceed 64 GiB");
         }
@@ -312,23 +358,13 @@ void loadTrained(memb_b200_reader& r)
     if (rows) {
         const uint64_t threads = uint64_t(rows) * 32;
         K::repack_rows_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, r.stream>>>(
-            dPacked, f.packedSize, dValueOffsets, dRowBytes, dRowOff16, rows, reinterpret_cast<uint32_t*>(dBlob));
+            dPacked, f.packedSize, dValueOffsets, dRowBytes, dRowOff16, rows, padBits,
+            reinterpret_cast<uint32_t*>(dBlob));
         ++g_launches;
         CUDA_CHECK(cudaGetLastError());
     }
 
-    // decode tables
-    const uint32_t maxLen = f.code.maxLen;
-    int64_t replicasOpt = g_optLutReplicas.load();
-    uint32_t replicas, lutBits;
-    if (replicasOpt == 32 || (replicasOpt == 0 && maxLen <= 9)) {
-        replicas = 32;
-        lutBits = std::max(1u, std::min(maxLen, 9u));
-    } else {
-        replicas = 1;
-        lutBits = std::max(1u, std::min(maxLen, 12u));
-    }
-    const std::vector<uint32_t> lut = buildLut(f.code, lutBits);
+    const std::vector<uint32_t> lut = buildLut(f.code, lutBits, symShift);
     uint32_t* dLut = deviceUpload(lut.data(), lut.size(), r.stats.device_bytes);
     r.owned.push_back(dLut);
 
@@ -342,20 +378,27 @@ void loadTrained(memb_b200_reader& r)
     p.dim = f.dim;
     p.lutBits = lutBits;
     p.lutReplicas = replicas;
-    p.lutShift = (replicas == 32 ? 25 : 30) - lutBits;
-    p.lutMask = ((1u << lutBits) - 1) << (replicas == 32 ? 7 : 2);
-    p.codebookSize = static_cast<uint32_t>(f.centroids.size());
-    p.rowWords = ((maxRowBytes + 15) / 16) * 4 + 4;
-    r.trainedEscape = maxLen > lutBits;
-    // symbols per window reload: G * maxLen <= 64 bits
-    const uint32_t allowed = 64 / std::max(maxLen, 1u);
-    r.trainedG = allowed >= 16 ? 16 : allowed >= 8 ? 8 : allowed >= 7 ? 7 : allowed >= 5 ? 5 : 4;
+    p.padBits = padBits;
+    p.lutMask = ((1u << lutBits) - 1) << padBits;
+    p.symShift = symShift;
+    p.codebookSize = codebookSize;
+    p.rowWords = maxRowUnits * 4 + 4;
+    r.trainedEscape = escape;
+    // symbols per window reload: G * maxLen <= 64 - padBits valid bits
+    const uint32_t allowed = (64 - padBits) / std::max(maxLen, 1u);
+    r.trainedG = escape ? 3 : allowed >= 16 ? 16 : allowed >= 8 ? 8 : allowed >= 7 ? 7 : allowed >= 6 ? 6 : 5;
 
-    const size_t fixedBytes = K::TRAINED_CODEBOOK_BYTES + K::trainedLutBytes(lutBits, replicas);
-    const size_t perWarp = K::trainedWarpBytes(p.rowWords);
+    // how many warps (tiles in flight) fit beside the tables in the shared window
+    r.smemBase = probeSmemBase(r.stream);
+    const uint32_t lutBytes = K::trainedLutBytes(lutBits, replicas);
+    const uint32_t perWarp = K::trainedWarpBytes(p.rowWords);
     uint32_t warps = 0;
-    if (r.smemOptin > fixedBytes) {
-        warps = static_cast<uint32_t>(std::min<size_t>(K::TRAINED_MAX_WARPS, (r.smemOptin - fixedBytes) / perWarp));
+    for (uint32_t w = 1; w <= K::TRAINED_MAX_WARPS; ++w) {
+        const K::TrainedLayout lay = K::trainedLayout(r.smemBase, lutBytes, perWarp, w);
+        if (lay.end - r.smemBase > r.smemOptin) {
+            break;
+        }
+        warps = w;
     }
     const int64_t warpsOpt = g_optWarps.load();
     if (warpsOpt > 0) {
@@ -431,13 +474,14 @@ bool vec4Ok(uint32_t dim, const K::OutputSpec& o)
            reinterpret_cast<uintptr_t>(o.out) % 16 == 0;
 }
 
-template <int G, bool VEC4, bool ESCAPE>
+template <int G, bool VEC4, bool ESCAPE, bool SMALLCB>
 void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
                          const K::OutputSpec& o, int epi, cudaStream_t stream)
 {
     const K::TrainedParams& p = r.trained;
-    const size_t smemBytes = K::TRAINED_CODEBOOK_BYTES + K::trainedLutBytes(p.lutBits, p.lutReplicas) +
-                             size_t(r.trainedWarps) * K::trainedWarpBytes(p.rowWords);
+    const K::TrainedLayout lay = K::trainedLayout(r.smemBase, K::trainedLutBytes(p.lutBits, p.lutReplicas),
+                                                  K::trainedWarpBytes(p.rowWords), r.trainedWarps);
+    const size_t smemBytes = lay.end - r.smemBase;
     const uint64_t tiles = (n + 31) / 32;
     const unsigned grid = static_cast<unsigned>(
         std::min<uint64_t>(static_cast<uint64_t>(r.numSMs), (tiles + r.trainedWarps - 1) / r.trainedWarps));
@@ -445,36 +489,50 @@ void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t
     if (tiles + 4ull * grid * r.trainedWarps >= 0xffffffffull) {
         fail(MEMB_B200_ERR_ARGUMENT, "decode: too many rows in one call");
     }
-    auto kernel = K::trained_decode_kernel<G, VEC4, ESCAPE>;
+    auto kernel = K::trained_decode_kernel<G, VEC4, ESCAPE, SMALLCB>;
     CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemBytes)));
     uint32_t* counter = r.dTileCounters + (const_cast<memb_b200_reader&>(r).launchSeq++ % memb_b200_reader::TILE_COUNTERS);
     CUDA_CHECK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), stream));
     kernel<<<grid, block, smemBytes, stream>>>(p, ids, rowBegin, n, o, epi, counter);
 }
 
+// Picks the instantiation: G symbols per window reload (loadTrained), and for the
+// 128-bit-store kernels whether the symbol field already is a codebook offset.
+// Odd shapes (scalar stores) always run G = 5, which is valid for every
+// non-escaping code (5 * 11 <= 57, 5 * 12 <= 62).
 template <bool VEC4>
 void launchTrainedG(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
                     const K::OutputSpec& o, int epi, cudaStream_t stream)
 {
     if (r.trainedEscape) {
-        launchTrainedKernel<4, VEC4, true>(r, ids, rowBegin, n, o, epi, stream);
+        launchTrainedKernel<3, VEC4, true, false>(r, ids, rowBegin, n, o, epi, stream);
         return;
     }
+    if (!VEC4) {
+        launchTrainedKernel<5, false, false, false>(r, ids, rowBegin, n, o, epi, stream);
+        return;
+    }
+    const bool small = r.trained.symShift == 2;
     switch (r.trainedG) {
     case 16:
-        launchTrainedKernel<16, VEC4, false>(r, ids, rowBegin, n, o, epi, stream);
+        small ? launchTrainedKernel<16, true, false, true>(r, ids, rowBegin, n, o, epi, stream)
+              : launchTrainedKernel<16, true, false, false>(r, ids, rowBegin, n, o, epi, stream);
         break;
     case 8:
-        launchTrainedKernel<8, VEC4, false>(r, ids, rowBegin, n, o, epi, stream);
+        small ? launchTrainedKernel<8, true, false, true>(r, ids, rowBegin, n, o, epi, stream)
+              : launchTrainedKernel<8, true, false, false>(r, ids, rowBegin, n, o, epi, stream);
         break;
     case 7:
-        launchTrainedKernel<7, VEC4, false>(r, ids, rowBegin, n, o, epi, stream);
+        small ? launchTrainedKernel<7, true, false, true>(r, ids, rowBegin, n, o, epi, stream)
+              : launchTrainedKernel<7, true, false, false>(r, ids, rowBegin, n, o, epi, stream);
         break;
-    case 5:
-        launchTrainedKernel<5, VEC4, false>(r, ids, rowBegin, n, o, epi, stream);
+    case 6:
+        small ? launchTrainedKernel<6, true, false, true>(r, ids, rowBegin, n, o, epi, stream)
+              : launchTrainedKernel<6, true, false, false>(r, ids, rowBegin, n, o, epi, stream);
         break;
     default:
-        launchTrainedKernel<4, VEC4, false>(r, ids, rowBegin, n, o, epi, stream);
+        small ? launchTrainedKernel<5, true, false, true>(r, ids, rowBegin, n, o, epi, stream)
+              : launchTrainedKernel<5, true, false, false>(r, ids, rowBegin, n, o, epi, stream);
         break;
     }
 }

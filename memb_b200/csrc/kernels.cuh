@@ -199,14 +199,17 @@ __global__ void measure_rows_kernel(const uint8_t* __restrict__ packed, uint64_t
     rowBytes[r] = static_cast<uint32_t>((bit + 7) >> 3);
 }
 
-// L0b.  Copy every row to its 16 B-aligned home in row-id order.  Words are
-// stored byte-swapped so that a plain 32-bit shared-memory load yields the
-// MSB-first bit order of src/bit_stream.h:18-34 without a PRMT in the hot loop.
-// One warp per row; tail bytes (and bytes past the end of the file) are zero.
+// L0b.  Copy every row to its 16 B-aligned home in row-id order, re-ordering the
+// bits for the decode kernel: the file packs codes MSB-first into bytes
+// (src/bit_stream.h:18-34); the blob holds the same bit sequence LSB-first in
+// 32-bit words and shifted up by padBits, i.e. stream bit k is bit (k + padBits) % 32
+// of word (k + padBits) / 32.  The decoder then indexes its LUT with `window & mask`
+// (no shift) and advances with one funnel shift.  One warp per row; tail bits (and
+// bytes past the end of the file, src/bit_stream_reader.h:22-25) are zero.
 __global__ void repack_rows_kernel(const uint8_t* __restrict__ packed, uint64_t packedSize,
                                    const uint32_t* __restrict__ valueOffsets,
                                    const uint32_t* __restrict__ rowBytes,
-                                   const uint32_t* __restrict__ rowOff16, uint32_t rows,
+                                   const uint32_t* __restrict__ rowOff16, uint32_t rows, uint32_t padBits,
                                    uint32_t* __restrict__ blob)
 {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) / WARP;
@@ -218,15 +221,24 @@ __global__ void repack_rows_kernel(const uint8_t* __restrict__ packed, uint64_t 
     const uint32_t bytes = rowBytes[warp];
     const uint32_t words = (rowOff16[warp + 1] - rowOff16[warp]) * 4;
     uint32_t* dst = blob + static_cast<uint64_t>(rowOff16[warp]) * 4;
-    for (uint32_t w = lane; w < words; w += WARP) {
+    // big-endian word `wi` of the row as stored in the file (zero outside the row)
+    auto fileWord = [&](int64_t wi) -> uint32_t {
         uint32_t v = 0;
+        if (wi >= 0) {
 #pragma unroll
-        for (uint32_t k = 0; k < 4; ++k) {
-            const uint32_t b = w * 4 + k;
-            const uint32_t byte = (b < bytes && src + b < packedSize) ? packed[src + b] : 0u;
-            v = (v << 8) | byte;
+            for (uint32_t k = 0; k < 4; ++k) {
+                const uint64_t b = static_cast<uint64_t>(wi) * 4 + k;
+                const uint32_t byte = (b < bytes && src + b < packedSize) ? packed[src + b] : 0u;
+                v = (v << 8) | byte;
+            }
         }
-        dst[w] = v;
+        return v;
+    };
+    for (uint32_t w = lane; w < words; w += WARP) {
+        // 32 stream bits starting at stream bit 32*w - padBits, MSB-first, then bit-reversed
+        const uint32_t cur = fileWord(w);
+        const uint32_t msbFirst = padBits ? __funnelshift_l(cur, fileWord(static_cast<int64_t>(w) - 1), 32 - padBits) : cur;
+        dst[w] = __brev(msbFirst);
     }
 }
 
@@ -241,31 +253,44 @@ __global__ void pad_rows16_kernel(const uint32_t* __restrict__ rowBytes, uint32_
 
 // ------------------------------------------------------------ K1 trained ----
 // HBM layout (built once at load):
-//   blob      rows in row-id order, each padded to 16 B, 32-bit words byte-swapped
+//   blob      rows in row-id order, each padded to 16 B.  Bits are stored LSB-first:
+//             stream bit k of a row (k-th bit in the MSB-first order of
+//             src/bit_stream.h:18-34) is bit (k + padBits) % 32 of word (k + padBits) / 32
 //   rowOff16  rows+1 offsets into blob in 16 B units
-//   lut       2^lutBits entries, entry = sym << 16 | escape << 15 | len
+//   lut       2^lutBits entries indexed by the next lutBits stream bits, first bit in
+//             bit 0 (i.e. the bit-reversed code prefix);
+//             entry = (sym << symShift) << 16 | escape << 15 | len
 //   codebook  centroids, fp32
 //
 // Work decomposition: one warp owns a tile of 32 consecutive OUTPUT rows; lane l
 // decodes row l of the tile serially (rows are independent byte-aligned streams,
 // SURVEY D1), all lanes in lock step on the symbol index.
 //
-// Shared memory is the scarce resource of this kernel (ncu r01: 73 % of the LSU
-// shared-memory wavefront rate, half of it bank conflicts), so every structure
-// is laid out so that lane l only ever touches bank l:
-//   codebook  [0, 1 KiB)            fp32 centroids
-//   lut       [1 KiB, ...)          entry i of replica l at i*128 + l*4 (32 replicas),
-//                                   or one plain copy when the code is too long
-//   per warp  rows[w][l]            word w of lane l's compressed row at (w*32+l)*4
-//             tile[r]               ring of the last 128 decoded SYMBOLS of row r, 132 B stride
-// Compressed rows reach shared memory through registers: each lane pulls its own
-// row with 128-bit loads (four in flight) and scatters the words down its bank.
-// The decode loop keeps a 64-bit MSB-first window in two registers, re-centred
-// from shared memory every G symbols (G*maxLen <= 64), looks a symbol up with
-// one conflict-free LDS and packs four symbols into one word of the tile.  The
-// fp32 gather from the codebook happens on the way OUT of the transpose tile, so
-// the serial per-symbol chain carries no float and every global store is a
-// 128-bit streaming store covering 128 contiguous bytes per 8 lanes.
+// The per-symbol dependency chain is what bounds this kernel (ncu r01: 35 % of
+// the stall samples are the LDS of the LUT lookup, 22 % fixed-latency ALU), so
+// the layout is chosen to make that chain LOP3 -> LDS -> SHF:
+//   * LSB-first bits: the LUT index is `window & mask`, no shift; the window
+//     advances with one funnel shift right;
+//   * padBits (7 for the bank-replicated LUT, 2 for a single copy) parks the
+//     window so that `window & mask` already is the byte offset of the entry;
+//   * the LUT sits at a shared-memory address aligned to its own size, so the
+//     base and the lane's replica are OR-ed in by the same LOP3.
+// Shared memory is the scarce resource, so every structure is laid out so that
+// lane l only ever touches bank l:
+//   codebook  1 KiB, 1 KiB-aligned   fp32 centroids (address = base | sym * 4)
+//   lut       aligned to its size    entry i of replica l at i*128 + l*4 (32 replicas),
+//                                    or one plain copy when the code is too long
+//   per warp  rows[w][l]             word w of lane l's compressed row at (w*32+l)*4
+//             tile[r]                ring of the last 128 decoded SYMBOLS of row r, 132 B stride
+// Warp buffers fill the space below and above the LUT.  Compressed rows reach
+// shared memory through registers: each lane pulls its own row with 128-bit
+// loads (a tile ahead) and scatters the words down its bank.  The decode loop
+// keeps a 64-bit window in two registers, re-centred from shared memory every G
+// symbols (G*maxLen <= 64 - padBits), looks a symbol up with one conflict-free
+// LDS and packs four symbols into one word of the tile.  The fp32 gather from the
+// codebook happens on the way OUT of the transpose tile, so the serial
+// per-symbol chain carries no float and every global store is a 128-bit
+// streaming store covering 128 contiguous bytes per 8 lanes.
 struct TrainedParams {
     const uint4* blob;
     const uint32_t* rowOff16;
@@ -276,8 +301,9 @@ struct TrainedParams {
     uint32_t dim;
     uint32_t lutBits;       // L
     uint32_t lutReplicas;   // 1 or 32
-    uint32_t lutShift;      // window -> byte offset:  (hi >> lutShift) & lutMask
-    uint32_t lutMask;
+    uint32_t padBits;       // 7 (32 replicas) or 2 (single copy)
+    uint32_t lutMask;       // ((1 << L) - 1) << padBits
+    uint32_t symShift;      // 2 when the codebook has <= 64 entries (symbol stored as byte offset), else 0
     uint32_t codebookSize;
     uint32_t rowWords;      // words reserved per staged row (max row units * 4 + 4)
 };
@@ -300,18 +326,51 @@ __host__ __device__ inline uint32_t trainedWarpBytes(uint32_t rowWords)
     return rowWords * 128 + TRAINED_TILE_BYTES;
 }
 
+// Where things live in the CTA's shared window, as ABSOLUTE shared addresses
+// (`base` = address of the first dynamic shared byte, 1 KiB on sm_100).
+struct TrainedLayout {
+    uint32_t codebook;   // 1 KiB aligned
+    uint32_t lut;        // aligned to lutBytes
+    uint32_t lowStart;   // warps [0, lowWarps) at lowStart + w * perWarp
+    uint32_t lowWarps;
+    uint32_t highStart;  // warps [lowWarps, ...) at highStart + (w - lowWarps) * perWarp
+    uint32_t end;        // first byte not used
+};
+__host__ __device__ inline TrainedLayout trainedLayout(uint32_t base, uint32_t lutBytes, uint32_t perWarp,
+                                                       uint32_t warps)
+{
+    TrainedLayout l;
+    l.codebook = (base + 1023u) & ~1023u;
+    l.lowStart = l.codebook + TRAINED_CODEBOOK_BYTES;
+    l.lut = (l.lowStart + lutBytes - 1) / lutBytes * lutBytes;
+    const uint32_t fit = (l.lut - l.lowStart) / perWarp;
+    l.lowWarps = fit < warps ? fit : warps;
+    l.highStart = l.lut + lutBytes;
+    l.end = l.highStart + (warps - l.lowWarps) * perWarp;
+    return l;
+}
+
 __device__ __forceinline__ uint32_t smemAddr(const void* p)
 {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
-// Slow path for a window whose code is longer than the LUT width.
-__device__ __noinline__ uint32_t escapeDecode(const CanonicalCode* __restrict__ code, uint32_t window)
+// First dynamic shared byte of a kernel without static shared memory (the host
+// sizes the launch with it; the decode kernel re-derives and checks it).
+__global__ void smem_base_probe_kernel(uint32_t* out)
+{
+    extern __shared__ __align__(128) unsigned char probeSmem[];
+    *out = smemAddr(probeSmem);
+}
+
+// Slow path for a window whose code is longer than the LUT width.  `window`
+// holds the next stream bits MSB-first (at least 16 valid).
+__device__ __noinline__ uint32_t escapeDecode(const CanonicalCode* __restrict__ code, uint32_t window, uint32_t symShift)
 {
     for (uint32_t l = code->minLen; l <= code->maxLen; ++l) {
         const uint32_t rel = (l ? (window >> (32 - l)) : 0u) - code->firstCode[l];
         if (rel < code->count[l]) {
-            return (static_cast<uint32_t>(code->keys[code->firstIndex[l] + rel]) << 16) | l;
+            return ((static_cast<uint32_t>(code->keys[code->firstIndex[l] + rel]) << symShift) << 16) | l;
         }
     }
     return 0;
@@ -358,25 +417,39 @@ __device__ __forceinline__ void stcsF4If(bool pred, void* ptr, float4 v)
         "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(static_cast<uint32_t>(pred))
         : "memory");
 }
+__device__ __forceinline__ void stcsF4(void* ptr, float4 v)
+{
+    asm volatile("st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(ptr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
 
-// Four centroids for the four symbols packed in s4 (cb = shared address of the codebook).
+// Four centroids for the four symbol fields packed in s4.  cb = shared address of
+// the codebook (1 KiB aligned).  SMALLCB: a field already is the byte offset
+// (sym * 4 <= 252), so one PRMT splices it under the upper bytes of cb.
+template <bool SMALLCB>
 __device__ __forceinline__ float4 gatherCentroids(uint32_t cb, uint32_t s4)
 {
     float4 v;
-    v.x = ldsF32(cb + ((s4 << 2) & 0x3fcu));
-    v.y = ldsF32(cb + ((s4 >> 6) & 0x3fcu));
-    v.z = ldsF32(cb + ((s4 >> 14) & 0x3fcu));
-    v.w = ldsF32(cb + ((s4 >> 22) & 0x3fcu));
+    if (SMALLCB) {
+        v.x = ldsF32(__byte_perm(s4, cb, 0x7650));
+        v.y = ldsF32(__byte_perm(s4, cb, 0x7651));
+        v.z = ldsF32(__byte_perm(s4, cb, 0x7652));
+        v.w = ldsF32(__byte_perm(s4, cb, 0x7653));
+    } else {
+        v.x = ldsF32(cb | ((s4 << 2) & 0x3fcu));
+        v.y = ldsF32(cb | ((s4 >> 6) & 0x3fcu));
+        v.z = ldsF32(cb | ((s4 >> 14) & 0x3fcu));
+        v.w = ldsF32(cb | ((s4 >> 22) & 0x3fcu));
+    }
     return v;
 }
 
-// Decode state of one lane.  lut / rows are shared-window addresses.
+// Decode state of one lane.  lutLane / rowLane are shared-window addresses.
 struct LaneDecoder {
-    uint32_t hi, lo;     // 64 valid bits of the row, MSB first
-    uint32_t consumed;   // low 16 bits: bits consumed in this row so far (junk above)
-    uint32_t lut;        // LUT base (+ nothing: the lane offset is OR-ed into the index)
-    uint32_t laneOr;     // lane * 4 when the LUT is replicated per bank, else 0
-    uint32_t lutShift, lutMask;
+    uint32_t lo, hi;     // window: bit 0 of lo = bit `consumed` of the re-packed row
+    uint32_t consumed;   // low 16 bits: stream bits consumed in this row so far (junk above)
+    uint32_t lutLane;    // LUT base | lane * 4 (bank-replicated LUT) or LUT base (single copy)
+    uint32_t lutMask;
     uint32_t rowLane;    // word w of this lane's compressed row lives at rowLane + w * 128
 };
 
@@ -386,23 +459,23 @@ __device__ __forceinline__ void reloadWindow(LaneDecoder& d)
 {
     const uint32_t a = d.rowLane + ((d.consumed << 2) & 0x3ff80u);
     const uint32_t w0 = ldsU32At<0>(a), w1 = ldsU32At<128>(a), w2 = ldsU32At<256>(a);
-    d.hi = __funnelshift_l(w1, w0, d.consumed);
-    d.lo = __funnelshift_l(w2, w1, d.consumed);
+    d.lo = __funnelshift_r(w0, w1, d.consumed);
+    d.hi = __funnelshift_r(w1, w2, d.consumed);
 }
 
-// One symbol: LUT entry for the top bits of the window, window advanced by the
-// code length.  Returns the entry (symbol in bits 16..23).
+// One symbol: LUT entry for the next bits of the window, window advanced by the
+// code length.  Returns the entry (symbol field in bits 16..23).
 template <bool ESCAPE>
-__device__ __forceinline__ uint32_t decodeSymbol(LaneDecoder& d, const CanonicalCode* __restrict__ code)
+__device__ __forceinline__ uint32_t decodeSymbol(LaneDecoder& d, const TrainedParams& p)
 {
-    uint32_t e = ldsU32(d.lut + (((d.hi >> d.lutShift) & d.lutMask) | d.laneOr));
+    uint32_t e = ldsU32((d.lo & d.lutMask) | d.lutLane);
     if (ESCAPE) {
         if (e & 0x8000u) {
-            e = escapeDecode(code, d.hi);
+            e = escapeDecode(p.code, __brev(d.lo >> p.padBits), p.symShift);
         }
     }
-    d.hi = __funnelshift_l(d.lo, d.hi, e);  // shift = e & 31 = code length
-    d.lo = d.lo << (e & 31);
+    d.lo = __funnelshift_r(d.lo, d.hi, e);  // shift = e & 31 = code length
+    d.hi = __funnelshift_r(d.hi, 0u, e);
     d.consumed += e;
     return e;
 }
@@ -410,7 +483,7 @@ __device__ __forceinline__ uint32_t decodeSymbol(LaneDecoder& d, const Canonical
 // NW words of four symbols each, fully unrolled, window re-centred every G
 // symbols; word q goes to tileWord + 4*q.
 template <int NW, int G, bool ESCAPE>
-__device__ __forceinline__ void decodeWords(LaneDecoder& d, const CanonicalCode* __restrict__ code, uint32_t tileWord)
+__device__ __forceinline__ void decodeWords(LaneDecoder& d, const TrainedParams& p, uint32_t tileWord)
 {
 #pragma unroll
     for (int q = 0; q < NW; ++q) {
@@ -420,8 +493,8 @@ __device__ __forceinline__ void decodeWords(LaneDecoder& d, const CanonicalCode*
             if ((q * 4 + k) % G == 0) {
                 reloadWindow(d);
             }
-            const uint32_t e = decodeSymbol<ESCAPE>(d, code);
-            // byte 2 of e (the symbol) -> byte k of acc
+            const uint32_t e = decodeSymbol<ESCAPE>(d, p);
+            // byte 2 of e (the symbol field) -> byte k of acc
             acc = __byte_perm(acc, e, k == 0 ? 0x3216 : k == 1 ? 0x3260 : k == 2 ? 0x3610 : 0x6210);
         }
         stsU32(tileWord + 4 * q, acc);
@@ -444,10 +517,18 @@ __device__ __forceinline__ uint4 loadRowUnit(const uint4* p)
     return v;
 }
 
-// G = symbols decoded per window reload (G * maxLen <= 64).  VEC4: dim, stride
-// and column offset are multiples of 4 and the output is 16 B aligned -> 128-bit
-// streaming stores.  ESCAPE: some code is longer than the LUT is wide.
-template <int G, bool VEC4, bool ESCAPE>
+__device__ __forceinline__ uint32_t shflFrom(uint32_t v, uint32_t srcLane)
+{
+    uint32_t r;
+    asm volatile("shfl.sync.idx.b32 %0, %1, %2, 0x1f, 0xffffffff;" : "=r"(r) : "r"(v), "r"(srcLane));
+    return r;
+}
+
+// G = symbols decoded per window reload (G * maxLen <= 64 - padBits).  VEC4: dim,
+// stride and column offset are multiples of 4 and the output is 16 B aligned ->
+// 128-bit streaming stores.  ESCAPE: some code is longer than the LUT is wide.
+// SMALLCB: symShift == 2 (see gatherCentroids).
+template <int G, bool VEC4, bool ESCAPE, bool SMALLCB>
 __global__ void __maxnreg__(TRAINED_MAX_REGS)
 trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, uint32_t rowBegin, uint64_t n,
                       const OutputSpec o, const int epi, uint32_t* __restrict__ tileCounter)
@@ -458,9 +539,16 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     const uint32_t warpsPerCta = blockDim.x / WARP;
 
     const uint32_t lutBytes = trainedLutBytes(p.lutBits, p.lutReplicas);
+    const uint32_t base = smemAddr(smem);
+    const TrainedLayout lay = trainedLayout(base, lutBytes, trainedWarpBytes(p.rowWords), warpsPerCta);
     {
-        float* cbS = reinterpret_cast<float*>(smem);
-        uint32_t* lutS = reinterpret_cast<uint32_t*>(smem + TRAINED_CODEBOOK_BYTES);
+        uint32_t dynBytes;
+        asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dynBytes));
+        if (lay.end - base > dynBytes) {
+            __trap();  // the host sized the launch for another shared-window base
+        }
+        float* cbS = reinterpret_cast<float*>(smem + (lay.codebook - base));
+        uint32_t* lutS = reinterpret_cast<uint32_t*>(smem + (lay.lut - base));
         const uint32_t entries = 1u << p.lutBits;
         if (p.lutReplicas == 1) {
             for (uint32_t i = threadIdx.x; i < entries; i += blockDim.x) {
@@ -478,16 +566,23 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     __syncthreads();
 
     // shared-window addresses
-    const uint32_t cb = smemAddr(smem);
-    const uint32_t warpBase = cb + TRAINED_CODEBOOK_BYTES + lutBytes + warp * trainedWarpBytes(p.rowWords);
+    const uint32_t cb = lay.codebook;
+    const uint32_t warpBase = warp < lay.lowWarps
+                                  ? lay.lowStart + warp * trainedWarpBytes(p.rowWords)
+                                  : lay.highStart + (warp - lay.lowWarps) * trainedWarpBytes(p.rowWords);
     const uint32_t tile = warpBase + p.rowWords * 128;  // 32 rows x 132 B of symbols (ring of two chunks)
     LaneDecoder d;
-    d.lut = cb + TRAINED_CODEBOOK_BYTES;
-    d.laneOr = p.lutReplicas == 1 ? 0u : lane * 4u;
-    d.lutShift = p.lutShift;
+    d.lutLane = lay.lut | (p.lutReplicas == 1 ? 0u : lane * 4u);
     d.lutMask = p.lutMask;
     d.rowLane = warpBase + lane * 4;
     const uint32_t tileLane = tile + lane * TRAINED_TILE_STRIDE;
+    // The flush reads ring slots it then does not store (units before the row in the
+    // first chunk, units past it in the last).  With SMALLCB a symbol byte IS a shared
+    // address offset, so those slots must never hold anything but multiples of 4.
+    for (uint32_t i = lane; i < TRAINED_TILE_BYTES / 4; i += WARP) {
+        stsU32(tile + i * 4, 0u);
+    }
+    __syncwarp();
 
     const uint64_t numTiles = (n + WARP - 1) / WARP;
     const uint32_t totalWarps = gridDim.x * warpsPerCta;
@@ -540,14 +635,21 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     // flight), t3 (id in flight); `ticket` is lane 0's pending atomicAdd result
     uint64_t t = static_cast<uint64_t>(blockIdx.x) * warpsPerCta + warp;
     uint64_t t1 = t + totalWarps, t2 = t1 + totalWarps, t3 = t2 + totalWarps;
-    uint32_t ticket = 0;
+    uint32_t ticket = 0, ticketLane = 0;
     auto drawTicket = [&]() {
-        if (lane == 0) {
-            ticket = atomicAdd(tileCounter, 1u);
-        }
-    };
-    auto redeemTicket = [&]() -> uint64_t {
-        return 4ull * totalWarps + __shfl_sync(0xffffffffu, ticket, 0);
+        // elect.sync + a predicated PTX atomic: atomicAdd() under `lane == 0` compiles to
+        // a warp-aggregated atomic whose broadcast shuffle waits for the L2 round trip on
+        // the spot (ncu r01: 10 % of all stall samples sat on that shuffle).  This way
+        // nothing touches `ticket` until it is redeemed a tile later.
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "elect.sync %1|p, 0xffffffff;\n"
+            "@p atom.global.add.u32 %0, [%2], 1;\n"
+            "}\n"
+            : "+r"(ticket), "=r"(ticketLane)
+            : "l"(tileCounter)
+            : "memory");
     };
     drawTicket();
     uint32_t offLo, offHi, offLoNext, offHiNext;
@@ -561,6 +663,10 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     prefetchRows(o16, units);
 
     while (t < numTiles) {
+        // The ticket drawn a tile ago is redeemed BEFORE this tile's loads are
+        // issued: ncu r01 showed the shuffle waiting on the scoreboard it shared
+        // with the loads issued just ahead of it (10 % of all stall samples).
+        const uint64_t t4 = 4ull * totalWarps + shflFrom(ticket, ticketLane);
         const uint32_t presentMask = __ballot_sync(0xffffffffu, present);
         // ---- stage: own row -> own bank ----
 #pragma unroll
@@ -597,20 +703,26 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                 }
             }
         }
-        // advance the pipeline: rows of t+1, offsets of t+2, id of t+3
+        // advance the pipeline: ticket of t+4, rows of t+1, offsets of t+2, id of t+3
+        drawTicket();
         const uint32_t o16Next = offLoNext, unitsNext = offHiNext - offLoNext;
         prefetchRows(o16Next, unitsNext);
         uint32_t offLoAfter, offHiAfter;
         const bool presentAfter = fetchOffsets(rowAfter, hasRow, offLoAfter, offHiAfter);
         rowAfter = fetchId(t3, hasRow);
-        const uint64_t t4 = redeemTicket();
-        drawTicket();
 
         d.hi = d.lo = 0;
         d.consumed = 0;
         const uint64_t row0 = t * WARP;
         const uint32_t rowsHere = static_cast<uint32_t>(min(static_cast<uint64_t>(WARP), n - row0));
         unsigned char* const outTile = reinterpret_cast<unsigned char*>(o.out + row0 * o.rowStride + o.colOffset);
+        // flush geometry of this tile: lane (fr, fq) serves rows fr, fr+2, ... ; row
+        // 2*it+fr starts aBase + it*aStep 16 B units into its 128 B line (mod 8)
+        unsigned char* const rowPtr0 = outTile + fr * rowBytes;
+        const uint32_t aBase = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(rowPtr0) >> 4);
+        const uint32_t aStep = static_cast<uint32_t>(rowBytes >> 3);  // two rows, in 16 B units
+        const uint32_t tileRows = tile + fr * TRAINED_TILE_STRIDE;
+        const bool fastFlush = VEC4 && presentMask == 0xffffffffu && epi == EPI_WRITE;
 
         for (uint32_t c0 = 0; c0 < dim; c0 += TRAINED_CHUNK) {
             const uint32_t nsym = min(TRAINED_CHUNK, dim - c0);
@@ -618,23 +730,23 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
             if (presentMask) {
                 uint32_t tw = tileLane + word0 * 4;
                 if (nsym == TRAINED_CHUNK) {
-                    decodeWords<TRAINED_CHUNK / 4, G, ESCAPE>(d, p.code, tw);
+                    decodeWords<TRAINED_CHUNK / 4, G, ESCAPE>(d, p, tw);
                 } else {
                     uint32_t nw = nsym / 4;
                     if (nw & 8) {
-                        decodeWords<8, G, ESCAPE>(d, p.code, tw);
+                        decodeWords<8, G, ESCAPE>(d, p, tw);
                         tw += 32;
                     }
                     if (nw & 4) {
-                        decodeWords<4, G, ESCAPE>(d, p.code, tw);
+                        decodeWords<4, G, ESCAPE>(d, p, tw);
                         tw += 16;
                     }
                     if (nw & 2) {
-                        decodeWords<2, G, ESCAPE>(d, p.code, tw);
+                        decodeWords<2, G, ESCAPE>(d, p, tw);
                         tw += 8;
                     }
                     if (nw & 1) {
-                        decodeWords<1, G, ESCAPE>(d, p.code, tw);
+                        decodeWords<1, G, ESCAPE>(d, p, tw);
                         tw += 4;
                     }
                     const uint32_t rest = nsym & 3;
@@ -642,7 +754,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                         reloadWindow(d);
                         uint32_t acc = 0;
                         for (uint32_t k = 0; k < rest; ++k) {
-                            const uint32_t e = decodeSymbol<ESCAPE>(d, p.code);
+                            const uint32_t e = decodeSymbol<ESCAPE>(d, p);
                             acc |= ((e >> 16) & 0xffu) << (8 * k);
                         }
                         stsU32(tw, acc);
@@ -659,33 +771,43 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                 const bool last = c0 + TRAINED_CHUNK >= dim;
                 const int unitsBefore = int(c0 / 4);
                 const int unitsAfter = int((c0 + nsym) / 4);
-                unsigned char* rowPtr = outTile + fr * rowBytes;
-                const uint32_t aBase = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(rowPtr) >> 4);
-                const uint32_t aStep = static_cast<uint32_t>(rowBytes >> 3);  // two rows, in 16 B units
-                const uint32_t tileRows = tile + fr * TRAINED_TILE_STRIDE;
-                if (presentMask == 0xffffffffu && epi == EPI_WRITE) {
-                    // common case, straight-line: 16 x (1 word of symbols -> 4 centroids -> 128-bit store);
-                    // the last chunk also drains the units the rows were lagging by (second pass)
-#pragma unroll
-                    for (uint32_t it = 0; it < 16; ++it) {
-                        const int a = int((aBase + it * aStep) & 7u);
-                        const int j = unitsBefore - a + int(fq);
-                        const int end = last ? unitsAfter : unitsAfter - a;
-                        const uint32_t s4 = ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j & 31) << 2));
-                        const float4 v = gatherCentroids(cb, s4);
-                        stcsF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr + it * 2 * rowBytes) + j, v);
-                    }
-                    if (last) {
+                if (fastFlush) {
+                    // common case, straight-line: 16 x (1 word of symbols -> 4 centroids -> 128-bit
+                    // store).  A middle chunk needs no predicate at all (the 16 units a lane
+                    // group covers are exactly the chunk, shifted by the row's lag); the
+                    // first chunk skips units before the row, the last one drains the lag.
+                    if (!last && c0 != 0) {
 #pragma unroll
                         for (uint32_t it = 0; it < 16; ++it) {
                             const int a = int((aBase + it * aStep) & 7u);
-                            const int j2 = unitsBefore - a + int(fq) + 16;
-                            const uint32_t t4 = ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j2 & 31) << 2));
-                            const float4 u = gatherCentroids(cb, t4);
-                            stcsF4If(j2 < unitsAfter, reinterpret_cast<float4*>(rowPtr + it * 2 * rowBytes) + j2, u);
+                            const int j = unitsBefore - a + int(fq);
+                            const uint32_t s4 = ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j & 31) << 2));
+                            const float4 v = gatherCentroids<SMALLCB>(cb, s4);
+                            stcsF4(reinterpret_cast<float4*>(rowPtr0 + it * 2 * rowBytes) + j, v);
+                        }
+                    } else {
+#pragma unroll
+                        for (uint32_t it = 0; it < 16; ++it) {
+                            const int a = int((aBase + it * aStep) & 7u);
+                            const int j = unitsBefore - a + int(fq);
+                            const int end = last ? unitsAfter : unitsAfter - a;
+                            const uint32_t s4 = ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j & 31) << 2));
+                            const float4 v = gatherCentroids<SMALLCB>(cb, s4);
+                            stcsF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * 2 * rowBytes) + j, v);
+                        }
+                        if (last) {
+#pragma unroll
+                            for (uint32_t it = 0; it < 16; ++it) {
+                                const int a = int((aBase + it * aStep) & 7u);
+                                const int j2 = unitsBefore - a + int(fq) + 16;
+                                const uint32_t s4 = ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j2 & 31) << 2));
+                                const float4 u = gatherCentroids<SMALLCB>(cb, s4);
+                                stcsF4If(j2 < unitsAfter, reinterpret_cast<float4*>(rowPtr0 + it * 2 * rowBytes) + j2, u);
+                            }
                         }
                     }
                 } else {
+                    unsigned char* rowPtr = rowPtr0;
                     for (uint32_t it = 0; it < 16; ++it) {
                         const uint32_t r = it * 2 + fr;
                         if (r < rowsHere) {
@@ -696,7 +818,8 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             for (int j = begin + int(fq); j < end; j += 16) {
                                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
                                 if (rowPresent) {
-                                    v = gatherCentroids(cb, ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j & 31) << 2)));
+                                    v = gatherCentroids<SMALLCB>(
+                                        cb, ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j & 31) << 2)));
                                 }
                                 float4* dst = reinterpret_cast<float4*>(rowPtr) + j;
                                 if (epi != EPI_WRITE) {
@@ -713,6 +836,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                     }
                 }
             } else {
+                const uint32_t fieldShift = 2u - p.symShift;  // symbol field -> byte offset into the codebook
                 for (uint32_t r = 0; r < rowsHere; ++r) {
                     const bool rowPresent = (presentMask >> r) & 1u;
                     const uint32_t tileRow = tile + r * TRAINED_TILE_STRIDE + word0 * 4;
@@ -721,7 +845,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                         float v = 0.f;
                         if (rowPresent) {
                             const uint32_t s4 = ldsU32(tileRow + (c & ~3u));
-                            v = ldsF32(cb + (((s4 >> (8 * (c & 3))) & 0xffu) << 2));
+                            v = ldsF32(cb + (((s4 >> (8 * (c & 3))) & 0xffu) << fieldShift));
                         }
                         if (epi != EPI_WRITE) {
                             v = applyEpilogue(v, dstRow[c], epi, o.divisor);
@@ -766,11 +890,12 @@ __global__ void trained_decode_generic_kernel(const TrainedParams p, const int32
     for (uint32_t c = 0; c < p.dim; ++c) {
         float v = 0.f;
         if (present) {
-            const uint64_t wi = bit >> 5;
-            const uint32_t sh = static_cast<uint32_t>(bit & 31);
+            const uint64_t pos = bit + p.padBits;  // stream bit k lives at bit k + padBits, LSB-first
+            const uint64_t wi = pos >> 5;
+            const uint32_t sh = static_cast<uint32_t>(pos & 31);
             const uint32_t w0 = wi < limitWords ? words[wi] : 0u;
             const uint32_t w1 = wi + 1 < limitWords ? words[wi + 1] : 0u;
-            const uint32_t window = __funnelshift_l(w1, w0, sh);
+            const uint32_t window = __brev(__funnelshift_r(w0, w1, sh));
             uint32_t len;
             const uint32_t idx = canonicalDecode(*p.code, window, len);
             bit += len;

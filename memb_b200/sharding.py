@@ -1,0 +1,110 @@
+"""Row-range sharding of the lookup over the GPUs of one box.
+
+Rows are independent byte-aligned streams, so the path shards with no data-path
+collective: the reference itself cuts a batch into `ceil(n / T)` contiguous
+chunks, one per host thread (src/reader.cpp:65-80), and proves that the cut never
+changes a bit (src/tests.cpp:90-113).  Here the same cut is made per GPU: every
+rank (one process per GPU, torch.distributed) holds a replica of the compressed
+table and decodes its own contiguous slice of the OUTPUT rows.
+
+The only collective is optional: `all_gather_rows` assembles the dense matrix on
+every rank (NCCL all-gather over NVLink on the GPU box; gloo in the CPU tests)
+when one device must hold all of it.  torch is imported lazily and is plumbing
+only (process group, device tensors); every row is decoded by the sm_100a
+kernels behind `_memb`.
+"""
+
+
+def shard_bounds(n, world_size):
+    """[begin_0, begin_1, ..., begin_G] with chunks of ceil(n / G) rows, the cut of
+    src/reader.cpp:65-80 (jobSize = ceil(n / numThreads); the tail ranks may be
+    short or empty)."""
+    if world_size < 1:
+        raise ValueError("world_size must be >= 1")
+    job = (n + world_size - 1) // world_size
+    return [min(n, g * job) for g in range(world_size + 1)]
+
+
+def shard_range(n, rank, world_size):
+    """(begin, end) of the rows rank `rank` owns."""
+    if not 0 <= rank < world_size:
+        raise ValueError("rank out of range")
+    bounds = shard_bounds(n, world_size)
+    return bounds[rank], bounds[rank + 1]
+
+
+def _rank_world(group=None):
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()):
+        return 0, 1
+    return dist.get_rank(group), dist.get_world_size(group)
+
+
+def all_gather_rows(local, n_total, group=None):
+    """Assemble the (n_total, dim) matrix from the per-rank slices of `shard_range`.
+
+    `local` is this rank's (end - begin, dim) tensor.  Slices are padded to the
+    common chunk size ceil(n / G) so that ONE all_gather_into_tensor moves
+    everything; the pad rows are cut off again.  Returns a tensor on local.device."""
+    import torch
+    import torch.distributed as dist
+
+    rank, world = _rank_world(group)
+    if world == 1:
+        return local
+    job = (n_total + world - 1) // world
+    dim = local.shape[1]
+    begin, end = shard_range(n_total, rank, world)
+    if local.shape[0] != end - begin:
+        raise ValueError("local slice has %d rows, rank %d owns %d" % (local.shape[0], rank, end - begin))
+    gathered = torch.empty((world * job, dim), dtype=local.dtype, device=local.device)
+    if local.shape[0] == job:
+        send = local.contiguous()
+    else:
+        send = gathered.new_zeros((job, dim))
+        send[: local.shape[0]] = local
+    dist.all_gather_into_tensor(gathered, send, group=group)
+    return gathered[:n_total]
+
+
+def decode_range_sharded(reader, begin=0, end=None, *, gather=False, group=None, out=None):
+    """Full-vocabulary decode (Reader.tokenizer_embedding / to_keyed_vectors path,
+    python/memb/reader.py:19-30,94-111) sharded by row range: this rank decodes its
+    slice of rows [begin, end) on its own GPU into a device tensor.
+
+    Returns (tensor, (slice_begin, slice_end)); with gather=True the tensor is the
+    whole (end - begin, dim) matrix on every rank (one NCCL all-gather)."""
+    import torch
+
+    rank, world = _rank_world(group)
+    rows = reader.rows
+    end = rows if end is None else end
+    lo, hi = shard_range(end - begin, rank, world)
+    device = torch.device("cuda", reader._impl.device())
+    if out is None:
+        out = torch.empty((hi - lo, reader.dim), dtype=torch.float32, device=device)
+    stream = torch.cuda.current_stream(device).cuda_stream
+    reader._impl.decode_range_into(begin + lo, begin + hi, out.data_ptr(), True, stream)
+    if gather:
+        return all_gather_rows(out, end - begin, group), (begin, end)
+    return out, (begin + lo, begin + hi)
+
+
+def batch_embedding_ids_sharded(reader, ids, *, gather=False, group=None):
+    """Batched lookup of row ids with the QUERIES sharded by rank: `ids` is the whole
+    batch (identical on every rank, int32 numpy or torch); this rank decodes rows
+    shard_range(len(ids), rank, world) of the output."""
+    import torch
+
+    rank, world = _rank_world(group)
+    n = len(ids)
+    lo, hi = shard_range(n, rank, world)
+    device = torch.device("cuda", reader._impl.device())
+    ids_t = torch.as_tensor(ids[lo:hi], dtype=torch.int32).to(device, non_blocking=True).contiguous()
+    out = torch.empty((hi - lo, reader.dim), dtype=torch.float32, device=device)
+    stream = torch.cuda.current_stream(device).cuda_stream
+    reader._impl.decode_ids_into(ids_t.data_ptr(), True, hi - lo, out.data_ptr(), True, stream)
+    if gather:
+        return all_gather_rows(out, n, group), (0, n)
+    return out, (lo, hi)
