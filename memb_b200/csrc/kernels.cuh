@@ -584,7 +584,8 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     }
     __syncwarp();
 
-    const uint64_t numTiles = (n + WARP - 1) / WARP;
+    // tile numbers fit 32 bits: the host refuses launches with tiles + 4 * warps >= 2^32
+    const uint32_t numTiles = static_cast<uint32_t>((n + WARP - 1) / WARP);
     const uint32_t totalWarps = gridDim.x * warpsPerCta;
     const uint32_t dim = p.dim;
     const uint32_t fr = lane >> 4, fq = lane & 15;  // flush role: 16 lanes per output row, two rows per store
@@ -602,8 +603,8 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     // decodes row 0 instead, which keeps it in lock step on valid data; its output
     // is forced to zero at the flush.
     // (the loaded id is only touched one tile later: nothing here consumes it)
-    auto fetchId = [&](uint64_t tt, bool& has) -> uint32_t {
-        const uint64_t i = tt * WARP + lane;
+    auto fetchId = [&](uint32_t tt, bool& has) -> uint32_t {
+        const uint64_t i = static_cast<uint64_t>(tt) * WARP + lane;
         has = tt < numTiles && i < n;
         if (!has) {
             return 0;
@@ -633,8 +634,8 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
 
     // tile queue of this warp: t (decoding), t1 (rows in flight), t2 (offsets in
     // flight), t3 (id in flight); `ticket` is lane 0's pending atomicAdd result
-    uint64_t t = static_cast<uint64_t>(blockIdx.x) * warpsPerCta + warp;
-    uint64_t t1 = t + totalWarps, t2 = t1 + totalWarps, t3 = t2 + totalWarps;
+    uint32_t t = blockIdx.x * warpsPerCta + warp;
+    uint32_t t1 = t + totalWarps, t2 = t1 + totalWarps, t3 = t2 + totalWarps;
     uint32_t ticket = 0, ticketLane = 0;
     auto drawTicket = [&]() {
         // elect.sync + a predicated PTX atomic: atomicAdd() under `lane == 0` compiles to
@@ -666,7 +667,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         // The ticket drawn a tile ago is redeemed BEFORE this tile's loads are
         // issued: ncu r01 showed the shuffle waiting on the scoreboard it shared
         // with the loads issued just ahead of it (10 % of all stall samples).
-        const uint64_t t4 = 4ull * totalWarps + shflFrom(ticket, ticketLane);
+        const uint32_t t4 = 4u * totalWarps + shflFrom(ticket, ticketLane);
         const uint32_t presentMask = __ballot_sync(0xffffffffu, present);
         // ---- stage: own row -> own bank ----
 #pragma unroll
@@ -713,7 +714,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
 
         d.hi = d.lo = 0;
         d.consumed = 0;
-        const uint64_t row0 = t * WARP;
+        const uint64_t row0 = static_cast<uint64_t>(t) * WARP;
         const uint32_t rowsHere = static_cast<uint32_t>(min(static_cast<uint64_t>(WARP), n - row0));
         unsigned char* const outTile = reinterpret_cast<unsigned char*>(o.out + row0 * o.rowStride + o.colOffset);
         // flush geometry of this tile: lane (fr, fq) serves rows fr, fr+2, ... ; row
