@@ -309,12 +309,15 @@ struct TrainedParams {
 };
 
 constexpr uint32_t TRAINED_CODEBOOK_BYTES = 1024;  // 256 centroids
-constexpr uint32_t TRAINED_CHUNK = 64;             // symbols decoded between two flushes
-constexpr uint32_t TRAINED_TILE_STRIDE = 132;      // bytes per tile row: ring of two chunks + 4 (bank skew)
+constexpr uint32_t TRAINED_CHUNK = 32;             // symbols decoded between two flushes
+constexpr uint32_t TRAINED_CHUNK_UNITS = TRAINED_CHUNK / 4;       // 16 B output units (= tile words) per chunk and row
+constexpr uint32_t TRAINED_RING_UNITS = 2 * TRAINED_CHUNK_UNITS;  // the tile keeps the last two chunks of every row
+constexpr uint32_t TRAINED_TILE_STRIDE = TRAINED_RING_UNITS * 4 + 4;  // bytes per tile row: ring + 4 (bank skew)
+constexpr uint32_t TRAINED_FLUSH_ROWS = 32 / TRAINED_CHUNK_UNITS;  // rows covered by one store instruction
 constexpr uint32_t TRAINED_TILE_BYTES = 32 * TRAINED_TILE_STRIDE;
 constexpr uint32_t TRAINED_MAX_DIM = 4095;  // consumed bits live in 16 bits: dim * 16 < 65536
-constexpr uint32_t TRAINED_MAX_WARPS = 12;  // three warps per scheduler ...
-constexpr uint32_t TRAINED_MAX_REGS = 168;  // ... each scheduler owns 16384 registers: 3 x 32 x 168 = 16128
+constexpr uint32_t TRAINED_MAX_WARPS = 10;  // measured optimum (sweep r01: 8 -> 2.98, 10 -> 3.22, 12 -> 3.10 G rows/s) ...
+constexpr uint32_t TRAINED_MAX_REGS = 168;  // ... up to three warps on a scheduler, which owns 16384 registers: 3 x 32 x 168 = 16128
 constexpr uint32_t TRAINED_PREFETCH_UNITS = 12;  // 192 B of the next row per lane held in registers
 
 __host__ __device__ inline uint32_t trainedLutBytes(uint32_t lutBits, uint32_t replicas)
@@ -588,7 +591,8 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     const uint32_t numTiles = static_cast<uint32_t>((n + WARP - 1) / WARP);
     const uint32_t totalWarps = gridDim.x * warpsPerCta;
     const uint32_t dim = p.dim;
-    const uint32_t fr = lane >> 4, fq = lane & 15;  // flush role: 16 lanes per output row, two rows per store
+    // flush role: CHUNK_UNITS lanes per output row, FLUSH_ROWS rows per store instruction
+    const uint32_t fr = lane / TRAINED_CHUNK_UNITS, fq = lane % TRAINED_CHUNK_UNITS;
     const uint64_t rowBytes = o.rowStride * 4;
 
     // Three-stage software pipeline over the warp's tiles (every stage is one HBM
@@ -717,17 +721,17 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         const uint64_t row0 = static_cast<uint64_t>(t) * WARP;
         const uint32_t rowsHere = static_cast<uint32_t>(min(static_cast<uint64_t>(WARP), n - row0));
         unsigned char* const outTile = reinterpret_cast<unsigned char*>(o.out + row0 * o.rowStride + o.colOffset);
-        // flush geometry of this tile: lane (fr, fq) serves rows fr, fr+2, ... ; row
-        // 2*it+fr starts aBase + it*aStep 16 B units into its 128 B line (mod 8)
+        // flush geometry of this tile: lane (fr, fq) serves rows fr, fr+FLUSH_ROWS, ... ; row
+        // FLUSH_ROWS*it+fr starts aBase + it*aStep 16 B units into its 128 B line (mod 8)
         unsigned char* const rowPtr0 = outTile + fr * rowBytes;
         const uint32_t aBase = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(rowPtr0) >> 4);
-        const uint32_t aStep = static_cast<uint32_t>(rowBytes >> 3);  // two rows, in 16 B units
+        const uint32_t aStep = static_cast<uint32_t>(rowBytes >> 4) * TRAINED_FLUSH_ROWS;  // FLUSH_ROWS rows, in 16 B units
         const uint32_t tileRows = tile + fr * TRAINED_TILE_STRIDE;
         const bool fastFlush = VEC4 && presentMask == 0xffffffffu && epi == EPI_WRITE;
 
         for (uint32_t c0 = 0; c0 < dim; c0 += TRAINED_CHUNK) {
             const uint32_t nsym = min(TRAINED_CHUNK, dim - c0);
-            const uint32_t word0 = (c0 / 4) & 31u;  // ring position of this chunk's first word (0 or 16)
+            const uint32_t word0 = (c0 / 4) & (TRAINED_RING_UNITS - 1);  // ring position of this chunk's first word
             if (presentMask) {
                 uint32_t tw = tileLane + word0 * 4;
                 if (nsym == TRAINED_CHUNK) {
@@ -779,48 +783,48 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                     // first chunk skips units before the row, the last one drains the lag.
                     if (!last && c0 != 0) {
 #pragma unroll
-                        for (uint32_t it = 0; it < 16; ++it) {
+                        for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
                             const int a = int((aBase + it * aStep) & 7u);
                             const int j = unitsBefore - a + int(fq);
-                            const uint32_t s4 = ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j & 31) << 2));
+                            const uint32_t s4 = ldsU32(tileRows + it * TRAINED_FLUSH_ROWS * TRAINED_TILE_STRIDE + ((j & (TRAINED_RING_UNITS - 1)) << 2));
                             const float4 v = gatherCentroids<SMALLCB>(cb, s4);
-                            stcsF4(reinterpret_cast<float4*>(rowPtr0 + it * 2 * rowBytes) + j, v);
+                            stcsF4(reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j, v);
                         }
                     } else {
 #pragma unroll
-                        for (uint32_t it = 0; it < 16; ++it) {
+                        for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
                             const int a = int((aBase + it * aStep) & 7u);
                             const int j = unitsBefore - a + int(fq);
                             const int end = last ? unitsAfter : unitsAfter - a;
-                            const uint32_t s4 = ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j & 31) << 2));
+                            const uint32_t s4 = ldsU32(tileRows + it * TRAINED_FLUSH_ROWS * TRAINED_TILE_STRIDE + ((j & (TRAINED_RING_UNITS - 1)) << 2));
                             const float4 v = gatherCentroids<SMALLCB>(cb, s4);
-                            stcsF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * 2 * rowBytes) + j, v);
+                            stcsF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j, v);
                         }
                         if (last) {
 #pragma unroll
-                            for (uint32_t it = 0; it < 16; ++it) {
+                            for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
                                 const int a = int((aBase + it * aStep) & 7u);
-                                const int j2 = unitsBefore - a + int(fq) + 16;
-                                const uint32_t s4 = ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j2 & 31) << 2));
+                                const int j2 = unitsBefore - a + int(fq) + int(TRAINED_CHUNK_UNITS);
+                                const uint32_t s4 = ldsU32(tileRows + it * TRAINED_FLUSH_ROWS * TRAINED_TILE_STRIDE + ((j2 & (TRAINED_RING_UNITS - 1)) << 2));
                                 const float4 u = gatherCentroids<SMALLCB>(cb, s4);
-                                stcsF4If(j2 < unitsAfter, reinterpret_cast<float4*>(rowPtr0 + it * 2 * rowBytes) + j2, u);
+                                stcsF4If(j2 < unitsAfter, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j2, u);
                             }
                         }
                     }
                 } else {
                     unsigned char* rowPtr = rowPtr0;
-                    for (uint32_t it = 0; it < 16; ++it) {
-                        const uint32_t r = it * 2 + fr;
+                    for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
+                        const uint32_t r = it * TRAINED_FLUSH_ROWS + fr;
                         if (r < rowsHere) {
                             const int a = int((aBase + it * aStep) & 7u);
                             const int begin = max(unitsBefore - a, 0);
                             const int end = last ? unitsAfter : unitsAfter - a;
                             const bool rowPresent = (presentMask >> r) & 1u;
-                            for (int j = begin + int(fq); j < end; j += 16) {
+                            for (int j = begin + int(fq); j < end; j += int(TRAINED_CHUNK_UNITS)) {
                                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
                                 if (rowPresent) {
                                     v = gatherCentroids<SMALLCB>(
-                                        cb, ldsU32(tileRows + it * 2 * TRAINED_TILE_STRIDE + ((j & 31) << 2)));
+                                        cb, ldsU32(tileRows + it * TRAINED_FLUSH_ROWS * TRAINED_TILE_STRIDE + ((j & (TRAINED_RING_UNITS - 1)) << 2)));
                                 }
                                 float4* dst = reinterpret_cast<float4*>(rowPtr) + j;
                                 if (epi != EPI_WRITE) {
@@ -833,7 +837,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                                 __stcs(dst, v);
                             }
                         }
-                        rowPtr += 2 * rowBytes;
+                        rowPtr += TRAINED_FLUSH_ROWS * rowBytes;
                     }
                 }
             } else {
