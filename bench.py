@@ -259,6 +259,21 @@ def measured_peak():
         return 6650.0, "fallback of B200_PROFILING.md (MEASURED_PEAKS.json absent)"
 
 
+def ncu_traffic(args):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the decode kernel from the
+    committed `ncu --set full` capture (profiles/), valid for the default workload only."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "k1_ncu_latest.json")) as f:
+            rec = json.load(f)
+        if (rec["rows"], rec["dim"], rec["bits"], rec["batch"]) == (args.rows, args.dim, args.bits, args.batch):
+            return {"bytes_per_launch": rec["dram_bytes_read"] + rec["dram_bytes_write"], "unit": "B",
+                    "dram_bytes_read": rec["dram_bytes_read"], "dram_bytes_write": rec["dram_bytes_write"],
+                    "source": rec["source"]}
+    except Exception:  # noqa: BLE001
+        pass
+    return None
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -346,6 +361,9 @@ def run_b200(args):
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / e2e_steps
     e2e_value = world * n / (e2e_ms / 1e3)
 
+    # ---- all ranks: configs[2], full-vocabulary decode sharded by row range (+ optional all-gather) ----
+    sharded = None if args.no_extra else sharded_full_vocab(reader, device, world, rank, barrier, max_over_ranks)
+
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -358,7 +376,7 @@ def run_b200(args):
     bytes_per_row = 4 * dim + payload_per_row + 4 + 4  # fp32 out + compressed row + value_offset + id
     achieved = n * bytes_per_row / (ms_step / 1e3) / 1e9
     roofline = {"bound": "hbm", "kernel": "trained_decode_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_source,
+                "frac": achieved / peak, "traffic": ncu_traffic(args), "peak_source": peak_source,
                 "algorithmic_bytes_per_row": bytes_per_row,
                 "write_only_frac": n * 4 * dim / (ms_step / 1e3) / 1e9 / peak,
                 "launch_ms": ms_step}
@@ -395,12 +413,54 @@ def run_b200(args):
     }
     if not args.no_extra:
         line["extra"] = extras(args, reader, device, peak)
+        bytes_per_row = 4 * dim + payload_per_row + 4
+        sharded["roofline_frac_per_gpu"] = (sharded["rows_per_s"] / world) * bytes_per_row / 1e9 / peak
+        line["extra"]["full_vocab_sharded"] = sharded
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     print(json.dumps(line), flush=True)
     if not parity:
         raise SystemExit("bench: GPU rows differ from the oracle")
+
+
+def sharded_full_vocab(reader, device, world, rank, barrier, max_over_ranks):
+    """configs[2]: every rank decodes its row range of the whole vocabulary (strong scaling:
+    total work fixed); then one NCCL all-gather so that every device holds the dense matrix.
+    Decode and gather are timed separately (max over ranks, CUDA events)."""
+    import torch
+
+    from memb_b200.sharding import all_gather_rows, decode_range_sharded, shard_range
+
+    rows, dim = reader.rows, reader.dim
+    lo, hi = shard_range(rows, rank, world)
+    out = torch.empty((hi - lo, dim), dtype=torch.float32, device=device)
+    for _ in range(3):
+        decode_range_sharded(reader, out=out)
+    barrier()
+    reps = 20
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    for _ in range(reps):
+        decode_range_sharded(reader, out=out)
+    stop.record()
+    barrier()
+    decode_ms = max_over_ranks(start.elapsed_time(stop)) / reps
+    result = {"rows": rows, "gpus": world, "decode_ms": decode_ms, "rows_per_s": rows / (decode_ms / 1e3),
+              "scaling": "strong", "gather_ms": None}
+    if world > 1:
+        gathered = all_gather_rows(out, rows)
+        barrier()
+        start.record()
+        for _ in range(5):
+            gathered = all_gather_rows(out, rows)
+        stop.record()
+        barrier()
+        result["gather_ms"] = max_over_ranks(start.elapsed_time(stop)) / 5
+        result["gather_gb_per_s_per_gpu"] = rows * dim * 4 * (world - 1) / world / (result["gather_ms"] / 1e3) / 1e9
+        del gathered
+    del out
+    return result
 
 
 def extras(args, reader, device, peak):

@@ -76,6 +76,7 @@ public:
     memb_b200_reader* handle() const { return impl_; }
     size_t dim() const { return memb_b200_dim(impl_); }
     size_t rows() const { return memb_b200_rows(impl_); }
+    int device() const { return memb_b200_device(impl_); }
 
     py::array_t<float> wordEmbedding(const std::string& word) const
     {
@@ -319,6 +320,7 @@ PYBIND11_MODULE(_memb, m)
         .def("keys", &Reader::keys)
         // additive
         .def("rows", &Reader::rows)
+        .def("device", &Reader::device)
         .def("resolve", &Reader::resolve)
         .def("batch_embedding_ids", &Reader::batchEmbeddingIds)
         .def("decode_range", &Reader::decodeRange)
