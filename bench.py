@@ -30,6 +30,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+_JSON_OUT = sys.stdout
 METRIC = "decoded rows/sec (fp32 output GB/s vs HBM peak) of the batched embedding lookup"
 UNIT = "rows/s"
 
@@ -246,7 +247,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "output_gb_per_s": value * args.dim * 4 / 1e9,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
 
 
 # ------------------------------------------------------------- B200 arm ----
@@ -419,7 +420,7 @@ def run_b200(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
     if not parity:
         raise SystemExit("bench: GPU rows differ from the oracle")
 
@@ -506,6 +507,12 @@ def extras(args, reader, device, peak):
 
 def main():
     args = parse_args()
+    # stdout carries exactly ONE JSON line: anything a library prints there (NCCL's version
+    # banner, for one) is sent to stderr instead
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
