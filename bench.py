@@ -53,15 +53,20 @@ def parse_args():
 
 
 # ------------------------------------------------------------- workload ----
-def table_path(args):
-    return os.path.join(args.cache_dir, "glove_shape_%d_x_%d_trained%d.bin" % (args.rows, args.dim, args.bits))
+def table_path(args, storage="trained", bits=None, seed=3, rows=None):
+    bits = args.bits if bits is None else bits
+    rows = args.rows if rows is None else rows
+    tag = "" if seed == 3 else "_s%d" % seed
+    return os.path.join(args.cache_dir, "glove_shape_%d_x_%d_%s%d%s.bin" % (rows, args.dim, storage, bits, tag))
 
 
-def build_table(args):
+def build_table(args, storage="trained", bits=None, seed=3, rows=None):
     """Synthetic GloVe-840B-shaped file through the repo's Builder (the memb_converter
-    equivalent): N(0,1) float32 vectors (PCG64 seed 3 per chunk), unique words in
+    equivalent): N(0,1) float32 vectors (PCG64 seed `seed` per chunk), unique words in
     shuffled insertion order.  Cached on disk; returns build seconds (0 when cached)."""
-    path = table_path(args)
+    bits = args.bits if bits is None else bits
+    rows = args.rows if rows is None else rows
+    path = table_path(args, storage, bits, seed, rows)
     if os.path.exists(path):
         return 0.0
     import memb_b200
@@ -69,20 +74,20 @@ def build_table(args):
 
     t0 = time.time()
     os.makedirs(args.cache_dir, exist_ok=True)
-    rows, dim = args.rows, args.dim
+    dim = args.dim
     matrix = np.empty((rows, dim), np.float32)
     chunks = max(1, min(32, os.cpu_count() or 1))
     bounds = np.linspace(0, rows, chunks + 1).astype(np.int64)
 
     def fill(i):
-        rng = np.random.Generator(np.random.PCG64([3, i]))
+        rng = np.random.Generator(np.random.PCG64([seed, i]))
         rng.standard_normal(out=matrix[bounds[i]:bounds[i + 1]], dtype=np.float32)
 
     with ThreadPoolExecutor(chunks) as pool:
         list(pool.map(fill, range(chunks)))
-    order = np.random.Generator(np.random.PCG64(33)).permutation(rows)
+    order = np.random.Generator(np.random.PCG64(30 + seed)).permutation(rows)
     words = ["w%x" % i for i in order]
-    builder = memb_b200.Builder(dim, "trained", args.bits)
+    builder = memb_b200.Builder(dim, storage, bits)
     builder.add_words(words, matrix)
     tmp = path + ".tmp%d" % os.getpid()
     builder.save(tmp)
@@ -417,6 +422,7 @@ def run_b200(args):
         bytes_per_row = 4 * dim + payload_per_row + 4
         sharded["roofline_frac_per_gpu"] = (sharded["rows_per_s"] / world) * bytes_per_row / 1e9 / peak
         line["extra"]["full_vocab_sharded"] = sharded
+        line["extra"].update(extra_configs(args, reader, device, peak))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -503,6 +509,88 @@ def extras(args, reader, device, peak):
                                        "kernel, decode, D2H into a fresh numpy array"}
     del got
     return result
+
+
+def _time_launches(fn, reps=20, warm=3):
+    import torch
+
+    for _ in range(warm):
+        fn()
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    start.record()
+    for _ in range(reps):
+        fn()
+    stop.record()
+    torch.cuda.synchronize()
+    return start.elapsed_time(stop) / reps
+
+
+def zipf_ids(rows, n, seed):
+    """Zipf(s = 1) over a random permutation of the rows: rank k drawn with p ~ 1/k
+    (inverse CDF of the continuous approximation), BASELINE.json configs[4]."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    ranks = np.minimum(np.exp(rng.random(n) * np.log(rows + 1.0)).astype(np.int64), rows) - 1
+    perm = rng.permutation(rows)
+    return perm[ranks].astype(np.int32)
+
+
+def extra_configs(args, reader, device, peak):
+    """BASELINE.json configs[3] and configs[4] on one GPU (rank 0): the uniform storage at 8 bits
+    (payload is one byte per weight whatever the bit width) and the fused ReadersUnion
+    of two trained 4-bit readers, average and concatenate, Zipf-distributed lookups."""
+    import torch
+
+    import memb_b200
+    from memb_b200 import _memb
+
+    out = {}
+    stream = torch.cuda.current_stream().cuda_stream
+    n, dim = args.batch, args.dim
+    ids = torch.from_numpy(batch_ids(args, 0)).to(device)
+
+    # ---- configs[3]: uniform, 2 M x dim ----
+    rows_u = min(args.rows, 2_000_000)
+    build_table(args, "uniform", 8, seed=5, rows=rows_u)
+    uni = memb_b200.Reader(table_path(args, "uniform", 8, 5, rows_u), device=device.index)
+    ids_u = torch.from_numpy(np.random.Generator(np.random.PCG64(41)).integers(0, rows_u, n).astype(np.int32)).to(device)
+    buf = torch.empty((max(n, rows_u), dim), dtype=torch.float32, device=device)
+    ms_ids = _time_launches(lambda: uni._impl.decode_ids_into(ids_u.data_ptr(), True, n, buf.data_ptr(), True, stream))
+    ms_all = _time_launches(lambda: uni._impl.decode_range_into(0, rows_u, buf.data_ptr(), True, stream))
+    per_row = 4 * dim + dim + 8
+    out["uniform_8bit"] = {
+        "rows": rows_u, "kernel": "uniform_decode_kernel",
+        "random_ids": {"n": n, "ms": ms_ids, "rows_per_s": n / (ms_ids / 1e3),
+                       "roofline_frac": n * (per_row + 4) / (ms_ids / 1e3) / 1e9 / peak},
+        "full_vocab": {"ms": ms_all, "rows_per_s": rows_u / (ms_all / 1e3),
+                       "roofline_frac": rows_u * per_row / (ms_all / 1e3) / 1e9 / peak},
+        "algorithmic_bytes_per_row": per_row}
+    del uni, buf
+
+    # ---- configs[4]: ReadersUnion of two trained readers, Zipf lookups ----
+    build_table(args, "trained", args.bits, seed=7)
+    second = memb_b200.Reader(table_path(args, "trained", args.bits, 7), device=device.index)
+    readers = [reader._impl, second._impl]
+    zipf = zipf_ids(args.rows, n, 8)
+    # row ids per reader, reader-major; the two vocabularies share their words here, so the same
+    # id addresses the same word in both
+    ids2 = torch.from_numpy(np.concatenate([zipf, zipf])).to(device)
+    payload = reader.load_stats()["payload_bytes"] / reader.rows + second.load_stats()["payload_bytes"] / second.rows
+    union = {}
+    for mode, cols in (("average", dim), ("concatenate", 2 * dim)):
+        buf = torch.empty((n, cols), dtype=torch.float32, device=device)
+        ms = _time_launches(lambda: _memb.union_decode_ids_into(readers, mode, ids2.data_ptr(), True, n,
+                                                                buf.data_ptr(), True, stream))
+        bytes_row = 4 * cols + payload + 2 * (4 + 4)
+        union[mode] = {"n": n, "ms": ms, "rows_per_s": n / (ms / 1e3), "out_columns": cols,
+                       "algorithmic_bytes_per_row": bytes_row,
+                       "roofline_frac": n * bytes_row / (ms / 1e3) / 1e9 / peak}
+        del buf
+    union["ids"] = "Zipf(s=1) over a permutation of the rows, PCG64 seed 8"
+    union["launches_per_call"] = 2
+    out["readers_union_2x_trained"] = union
+    del second, ids, ids2
+    return out
 
 
 def main():

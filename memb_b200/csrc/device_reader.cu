@@ -474,7 +474,7 @@ bool vec4Ok(uint32_t dim, const K::OutputSpec& o)
            reinterpret_cast<uintptr_t>(o.out) % 16 == 0;
 }
 
-template <int G, bool VEC4, bool ESCAPE, bool SMALLCB>
+template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW>
 void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
                          const K::OutputSpec& o, int epi, cudaStream_t stream)
 {
@@ -489,50 +489,59 @@ void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t
     if (tiles + 4ull * grid * r.trainedWarps >= 0xffffffffull) {
         fail(MEMB_B200_ERR_ARGUMENT, "decode: too many rows in one call");
     }
-    auto kernel = K::trained_decode_kernel<G, VEC4, ESCAPE, SMALLCB>;
+    auto kernel = K::trained_decode_kernel<G, VEC4, ESCAPE, SMALLCB, RMW>;
     CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemBytes)));
     uint32_t* counter = r.dTileCounters + (const_cast<memb_b200_reader&>(r).launchSeq++ % memb_b200_reader::TILE_COUNTERS);
     CUDA_CHECK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), stream));
     kernel<<<grid, block, smemBytes, stream>>>(p, ids, rowBegin, n, o, epi, counter);
 }
 
-// Picks the instantiation: G symbols per window reload (loadTrained), and for the
-// 128-bit-store kernels whether the symbol field already is a codebook offset.
-// Odd shapes (scalar stores) always run G = 5, which is valid for every
-// non-escaping code (5 * 11 <= 57, 5 * 12 <= 62).
+// Picks the instantiation: G symbols per window reload (loadTrained); for the
+// 128-bit-store kernels whether the symbol field already is a codebook offset and
+// whether the launch carries an average epilogue.  Odd shapes (scalar stores) always
+// run G = 5, which is valid for every non-escaping code (5 * 11 <= 57, 5 * 12 <= 62).
+template <int G>
+void launchTrainedVec(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
+                      const K::OutputSpec& o, int epi, cudaStream_t stream)
+{
+    const bool small = r.trained.symShift == 2;
+    const bool rmw = epi != K::EPI_WRITE;
+    if (small) {
+        rmw ? launchTrainedKernel<G, true, false, true, true>(r, ids, rowBegin, n, o, epi, stream)
+            : launchTrainedKernel<G, true, false, true, false>(r, ids, rowBegin, n, o, epi, stream);
+    } else {
+        rmw ? launchTrainedKernel<G, true, false, false, true>(r, ids, rowBegin, n, o, epi, stream)
+            : launchTrainedKernel<G, true, false, false, false>(r, ids, rowBegin, n, o, epi, stream);
+    }
+}
+
 template <bool VEC4>
 void launchTrainedG(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
                     const K::OutputSpec& o, int epi, cudaStream_t stream)
 {
     if (r.trainedEscape) {
-        launchTrainedKernel<3, VEC4, true, false>(r, ids, rowBegin, n, o, epi, stream);
+        launchTrainedKernel<3, VEC4, true, false, false>(r, ids, rowBegin, n, o, epi, stream);
         return;
     }
     if (!VEC4) {
-        launchTrainedKernel<5, false, false, false>(r, ids, rowBegin, n, o, epi, stream);
+        launchTrainedKernel<5, false, false, false, false>(r, ids, rowBegin, n, o, epi, stream);
         return;
     }
-    const bool small = r.trained.symShift == 2;
     switch (r.trainedG) {
     case 16:
-        small ? launchTrainedKernel<16, true, false, true>(r, ids, rowBegin, n, o, epi, stream)
-              : launchTrainedKernel<16, true, false, false>(r, ids, rowBegin, n, o, epi, stream);
+        launchTrainedVec<16>(r, ids, rowBegin, n, o, epi, stream);
         break;
     case 8:
-        small ? launchTrainedKernel<8, true, false, true>(r, ids, rowBegin, n, o, epi, stream)
-              : launchTrainedKernel<8, true, false, false>(r, ids, rowBegin, n, o, epi, stream);
+        launchTrainedVec<8>(r, ids, rowBegin, n, o, epi, stream);
         break;
     case 7:
-        small ? launchTrainedKernel<7, true, false, true>(r, ids, rowBegin, n, o, epi, stream)
-              : launchTrainedKernel<7, true, false, false>(r, ids, rowBegin, n, o, epi, stream);
+        launchTrainedVec<7>(r, ids, rowBegin, n, o, epi, stream);
         break;
     case 6:
-        small ? launchTrainedKernel<6, true, false, true>(r, ids, rowBegin, n, o, epi, stream)
-              : launchTrainedKernel<6, true, false, false>(r, ids, rowBegin, n, o, epi, stream);
+        launchTrainedVec<6>(r, ids, rowBegin, n, o, epi, stream);
         break;
     default:
-        small ? launchTrainedKernel<5, true, false, true>(r, ids, rowBegin, n, o, epi, stream)
-              : launchTrainedKernel<5, true, false, false>(r, ids, rowBegin, n, o, epi, stream);
+        launchTrainedVec<5>(r, ids, rowBegin, n, o, epi, stream);
         break;
     }
 }

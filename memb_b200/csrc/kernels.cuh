@@ -420,6 +420,31 @@ __device__ __forceinline__ void stcsF4If(bool pred, void* ptr, float4 v)
         "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(static_cast<uint32_t>(pred))
         : "memory");
 }
+// 128-bit load of the value an average epilogue adds to, executed only when `pred`.
+__device__ __forceinline__ float4 ldF4If(bool pred, const void* ptr)
+{
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.u32 p, %5, 0;\n"
+        "@p ld.global.v4.f32 {%0, %1, %2, %3}, [%4];\n"
+        "}\n"
+        : "+f"(v.x), "+f"(v.y), "+f"(v.z), "+f"(v.w)
+        : "l"(ptr), "r"(static_cast<uint32_t>(pred))
+        : "memory");
+    return v;
+}
+__device__ __forceinline__ void prefetchL2If(bool pred, const void* ptr)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.u32 p, %1, 0;\n"
+        "@p prefetch.global.L2 [%0];\n"
+        "}\n" ::"l"(ptr),
+        "r"(static_cast<uint32_t>(pred)));
+}
 __device__ __forceinline__ void stcsF4(void* ptr, float4 v)
 {
     asm volatile("st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(ptr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
@@ -513,6 +538,22 @@ __device__ __forceinline__ float applyEpilogue(float v, float old, int epi, floa
     return epi == EPI_ACCUMULATE ? s : __fdiv_rn(s, divisor);
 }
 
+// np.mean's add chain on four lanes of a row: old + v, and for the last reader / R.
+__device__ __forceinline__ float4 applyEpilogue4(float4 v, float4 old, int epi, float divisor)
+{
+    v.x = __fadd_rn(old.x, v.x);
+    v.y = __fadd_rn(old.y, v.y);
+    v.z = __fadd_rn(old.z, v.z);
+    v.w = __fadd_rn(old.w, v.w);
+    if (epi == EPI_FINALIZE) {
+        v.x = __fdiv_rn(v.x, divisor);
+        v.y = __fdiv_rn(v.y, divisor);
+        v.z = __fdiv_rn(v.z, divisor);
+        v.w = __fdiv_rn(v.w, divisor);
+    }
+    return v;
+}
+
 __device__ __forceinline__ uint4 loadRowUnit(const uint4* p)
 {
     uint4 v;
@@ -531,7 +572,9 @@ __device__ __forceinline__ uint32_t shflFrom(uint32_t v, uint32_t srcLane)
 // stride and column offset are multiples of 4 and the output is 16 B aligned ->
 // 128-bit streaming stores.  ESCAPE: some code is longer than the LUT is wide.
 // SMALLCB: symShift == 2 (see gatherCentroids).
-template <int G, bool VEC4, bool ESCAPE, bool SMALLCB>
+// RMW: the launch carries an average epilogue (ACCUMULATE / FINALIZE): the fast flush
+// reads the running sum, adds, divides for the last reader, and stores.
+template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW>
 __global__ void __maxnreg__(TRAINED_MAX_REGS)
 trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, uint32_t rowBegin, uint64_t n,
                       const OutputSpec o, const int epi, uint32_t* __restrict__ tileCounter)
@@ -727,11 +770,22 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         const uint32_t aBase = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(rowPtr0) >> 4);
         const uint32_t aStep = static_cast<uint32_t>(rowBytes >> 4) * TRAINED_FLUSH_ROWS;  // FLUSH_ROWS rows, in 16 B units
         const uint32_t tileRows = tile + fr * TRAINED_TILE_STRIDE;
-        const bool fastFlush = VEC4 && presentMask == 0xffffffffu && epi == EPI_WRITE;
+        const bool fastFlush = VEC4 && presentMask == 0xffffffffu && (RMW ? epi != EPI_WRITE : epi == EPI_WRITE);
 
         for (uint32_t c0 = 0; c0 < dim; c0 += TRAINED_CHUNK) {
             const uint32_t nsym = min(TRAINED_CHUNK, dim - c0);
             const uint32_t word0 = (c0 / 4) & (TRAINED_RING_UNITS - 1);  // ring position of this chunk's first word
+            if (RMW && fastFlush) {
+                // the flush of this chunk will read these 16 B units of the running sum
+                const int ub = int(c0 / 4);
+                const int ua = int((c0 + nsym) / 4);
+#pragma unroll
+                for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
+                    const int a = int((aBase + it * aStep) & 7u);
+                    const int j = ub - a + int(fq);
+                    prefetchL2If(j >= 0 && j < ua, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j);
+                }
+            }
             if (presentMask) {
                 uint32_t tw = tileLane + word0 * 4;
                 if (nsym == TRAINED_CHUNK) {
@@ -776,7 +830,34 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                 const bool last = c0 + TRAINED_CHUNK >= dim;
                 const int unitsBefore = int(c0 / 4);
                 const int unitsAfter = int((c0 + nsym) / 4);
-                if (fastFlush) {
+                if (fastFlush && RMW) {
+                    // average epilogue, straight-line: the running sums of the chunk were
+                    // pulled into L2 while the chunk was being decoded; load them all, then
+                    // gather, add (divide for the last reader) and store.  A second pass
+                    // drains the lagging units after the last chunk.
+                    const int passes = last ? 2 : 1;
+                    for (int pass = 0; pass < passes; ++pass) {
+                        const int shift = pass * int(TRAINED_CHUNK_UNITS);
+                        const int end0 = last ? unitsAfter : 0x7fffffff;
+                        float4 old[TRAINED_CHUNK_UNITS];
+#pragma unroll
+                        for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
+                            const int a = int((aBase + it * aStep) & 7u);
+                            const int j = unitsBefore - a + int(fq) + shift;
+                            const int end = last ? end0 : unitsAfter - a;
+                            old[it] = ldF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j);
+                        }
+#pragma unroll
+                        for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
+                            const int a = int((aBase + it * aStep) & 7u);
+                            const int j = unitsBefore - a + int(fq) + shift;
+                            const int end = last ? end0 : unitsAfter - a;
+                            const uint32_t s4 = ldsU32(tileRows + it * TRAINED_FLUSH_ROWS * TRAINED_TILE_STRIDE + ((j & (TRAINED_RING_UNITS - 1)) << 2));
+                            const float4 v = applyEpilogue4(gatherCentroids<SMALLCB>(cb, s4), old[it], epi, o.divisor);
+                            stcsF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j, v);
+                        }
+                    }
+                } else if (fastFlush) {
                     // common case, straight-line: 16 x (1 word of symbols -> 4 centroids -> 128-bit
                     // store).  A middle chunk needs no predicate at all (the 16 units a lane
                     // group covers are exactly the chunk, shifted by the row's lag); the
