@@ -549,23 +549,26 @@ def extra_configs(args, reader, device, peak):
     n, dim = args.batch, args.dim
     ids = torch.from_numpy(batch_ids(args, 0)).to(device)
 
-    # ---- configs[3]: uniform, 2 M x dim ----
+    # ---- configs[3]: uniform, 2 M x dim; the payload is one byte per weight at every bit width, so the
+    # sweep only changes the divisor: levels = 16 (a power of two: exact multiply) and 255 (IEEE divide) ----
     rows_u = min(args.rows, 2_000_000)
-    build_table(args, "uniform", 8, seed=5, rows=rows_u)
-    uni = memb_b200.Reader(table_path(args, "uniform", 8, 5, rows_u), device=device.index)
     ids_u = torch.from_numpy(np.random.Generator(np.random.PCG64(41)).integers(0, rows_u, n).astype(np.int32)).to(device)
     buf = torch.empty((max(n, rows_u), dim), dtype=torch.float32, device=device)
-    ms_ids = _time_launches(lambda: uni._impl.decode_ids_into(ids_u.data_ptr(), True, n, buf.data_ptr(), True, stream))
-    ms_all = _time_launches(lambda: uni._impl.decode_range_into(0, rows_u, buf.data_ptr(), True, stream))
     per_row = 4 * dim + dim + 8
-    out["uniform_8bit"] = {
-        "rows": rows_u, "kernel": "uniform_decode_kernel",
-        "random_ids": {"n": n, "ms": ms_ids, "rows_per_s": n / (ms_ids / 1e3),
-                       "roofline_frac": n * (per_row + 4) / (ms_ids / 1e3) / 1e9 / peak},
-        "full_vocab": {"ms": ms_all, "rows_per_s": rows_u / (ms_all / 1e3),
-                       "roofline_frac": rows_u * per_row / (ms_all / 1e3) / 1e9 / peak},
-        "algorithmic_bytes_per_row": per_row}
-    del uni, buf
+    for bits in (4, 8):
+        build_table(args, "uniform", bits, seed=5, rows=rows_u)
+        uni = memb_b200.Reader(table_path(args, "uniform", bits, 5, rows_u), device=device.index)
+        ms_ids = _time_launches(lambda: uni._impl.decode_ids_into(ids_u.data_ptr(), True, n, buf.data_ptr(), True, stream))
+        ms_all = _time_launches(lambda: uni._impl.decode_range_into(0, rows_u, buf.data_ptr(), True, stream))
+        out["uniform_%dbit" % bits] = {
+            "rows": rows_u, "kernel": "uniform_decode_kernel",
+            "random_ids": {"n": n, "ms": ms_ids, "rows_per_s": n / (ms_ids / 1e3),
+                           "roofline_frac": n * (per_row + 4) / (ms_ids / 1e3) / 1e9 / peak},
+            "full_vocab": {"ms": ms_all, "rows_per_s": rows_u / (ms_all / 1e3),
+                           "roofline_frac": rows_u * per_row / (ms_all / 1e3) / 1e9 / peak},
+            "algorithmic_bytes_per_row": per_row}
+        del uni
+    del buf
 
     # ---- configs[4]: ReadersUnion of two trained readers, Zipf lookups ----
     build_table(args, "trained", args.bits, seed=7)

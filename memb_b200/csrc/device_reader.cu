@@ -443,6 +443,11 @@ void loadUniform(memb_b200_reader& r)
     // quantization_levels is a uint8 promoted to float in the reference's
     // `... * floatValue / quantizationLevels` (src/uniform_compression.cpp:68-72)
     r.uniform.levels = static_cast<float>(f.quantizationLevels);
+    const uint32_t q = f.quantizationLevels;
+    // how `/ levels` is evaluated on the device (kernels.cuh: divideByLevels); every mode is
+    // the correctly rounded quotient
+    r.uniform.divMode = (q != 0 && (q & (q - 1)) == 0) ? 1 : (q == 255 ? 2 : 0);
+    r.uniform.invLevels = q ? 1.0f / static_cast<float>(q) : 0.0f;
     r.stats.upload_ms += msSince(t0);
     std::vector<uint8_t>().swap(f.uniformValues);
     std::vector<float>().swap(f.uniformMin);

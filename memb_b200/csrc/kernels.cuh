@@ -994,6 +994,54 @@ __global__ void trained_decode_generic_kernel(const TrainedParams p, const int32
     }
 }
 
+// Row-major walk over the n x perRow output elements (16 B units or floats) of K2/K3.
+// A block takes 32 consecutive output rows at a time and spreads their elements over its
+// threads, so every warp store covers 512 contiguous bytes and (row, column) come from a
+// multiply-high instead of a 64-bit division per element.  Elements are handled in batches
+// of K per thread in two phases -- `load` issues the (dependent: id -> row -> payload)
+// global loads of all K elements, `finish` computes and stores -- because with one element
+// in flight per thread the kernels were bound by the two HBM round trips per element
+// (r01: 3.0 TB/s of stores at 2048 threads/SM), not by bandwidth.
+template <int K, class State, class Load, class Finish>
+__device__ __forceinline__ void forEachElement(uint64_t n, uint32_t perRow, Load load, Finish finish)
+{
+    if (perRow > 1 && perRow < 2048) {
+        // floor(t / perRow) == umulhi(t, ceil(2^32 / perRow)) for t < 2^21 (t < 32 * 2048 here)
+        const uint32_t inv = 0xffffffffu / perRow + 1;
+        for (uint64_t rowBase = static_cast<uint64_t>(blockIdx.x) * 32; rowBase < n;
+             rowBase += static_cast<uint64_t>(gridDim.x) * 32) {
+            const uint32_t rowsHere = static_cast<uint32_t>(min(static_cast<uint64_t>(32), n - rowBase));
+            const uint32_t elems = rowsHere * perRow;
+            for (uint32_t t0 = threadIdx.x; t0 < elems; t0 += K * blockDim.x) {
+                State st[K];
+#pragma unroll
+                for (int k = 0; k < K; ++k) {
+                    const uint32_t t = t0 + k * blockDim.x;
+                    if (t < elems) {
+                        const uint32_t r = __umulhi(t, inv);
+                        st[k] = load(rowBase + r, t - r * perRow);
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < K; ++k) {
+                    if (t0 + k * blockDim.x < elems) {
+                        finish(st[k]);
+                    }
+                }
+            }
+        }
+    } else {
+        const uint64_t total = n * perRow;
+        for (uint64_t e = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; e < total;
+             e += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+            const uint64_t i = e / perRow;
+            finish(load(i, static_cast<uint32_t>(e - i * perRow)));
+        }
+    }
+}
+
+constexpr int FLAT_BATCH = 4;  // elements in flight per thread in K2/K3
+
 // ------------------------------------------------------------ K2 uniform ----
 // values: rows x dim bytes (dense, flattened at load from the per-word tables),
 // minmax: rows x (min, max).  out[i] = min + (max - min) * float(v) / levels,
@@ -1005,61 +1053,98 @@ struct UniformParams {
     uint32_t rows;
     uint32_t dim;
     float levels;
+    float invLevels;  // mode 1: 1 / levels exactly (levels a power of two); mode 2: RN(1 / levels)
+    int divMode;      // 0: IEEE divide, 1: exact multiply, 2: constant-divisor FMA sequence (levels == 255)
 };
 
-__device__ __forceinline__ float uniformDequant(float mn, float range, uint32_t v, float levels)
+// scaled / levels, correctly rounded (binary32, round to nearest even) in every mode:
+//   1  levels = 2^k: x * 2^-k is the same correctly rounded real number as x / 2^k
+//   2  levels = 255 (what the format's writer stores for 8 bits, min(1 << bits, 255),
+//      src/uniform_compression.cpp:5-8): q0 = x * RN(1/255), one FMA residual, one FMA
+//      correction.  Verified EXHAUSTIVELY on the host against x / 255.0f for every float
+//      with 1e-20 < |x| < 1e20 and for +0 (scripts/div255_exhaustive.c: 0 mismatches of
+//      2.25e9); anything outside that range takes the IEEE divide.
+//   0  any other divisor: IEEE divide.
+// The IEEE divide sequence made the 8-bit sweep ALU-bound (r01: 57 % of HBM against 80 %
+// for the power-of-two widths).
+__device__ __forceinline__ float divideByLevels(float x, const float levels, const float invLevels, const int divMode)
 {
-    return __fadd_rn(mn, __fdiv_rn(__fmul_rn(range, static_cast<float>(v)), levels));
+    if (divMode == 1) {
+        return __fmul_rn(x, invLevels);
+    }
+    if (divMode == 2) {
+        const float q0 = __fmul_rn(x, invLevels);
+        const float e = __fmaf_rn(-q0, levels, x);
+        const float q1 = __fmaf_rn(e, invLevels, q0);
+        const float ax = fabsf(x);
+        if ((ax > 1e-20f && ax < 1e20f) || __float_as_uint(x) == 0u) {
+            return q1;
+        }
+    }
+    return __fdiv_rn(x, levels);
 }
 
-// One thread per output float4 (VEC4) or per output float; output elements are
-// numbered row-major so every warp store is 512 contiguous bytes.
+__device__ __forceinline__ float uniformDequant(float mn, float range, uint32_t v, const float levels,
+                                                const float invLevels, const int divMode)
+{
+    return __fadd_rn(mn, divideByLevels(__fmul_rn(range, static_cast<float>(v)), levels, invLevels, divMode));
+}
+
+struct UniformState {
+    float* dst;
+    float2 mm;
+    uint32_t packed;  // four quantised values (VEC4) or one
+    bool present;
+};
+
 template <bool VEC4, int EPI>
 __global__ void uniform_decode_kernel(const UniformParams p, const int32_t* __restrict__ ids, uint32_t rowBegin,
                                       uint64_t n, const OutputSpec o)
 {
     const uint32_t perRow = VEC4 ? p.dim / 4 : p.dim;
-    const uint64_t total = n * perRow;
-    for (uint64_t e = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; e < total;
-         e += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
-        const uint64_t i = e / perRow;
-        const uint32_t c = static_cast<uint32_t>(e - i * perRow);
-        const int64_t row = ids ? static_cast<int64_t>(ids[i]) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
-        const bool present = row >= 0 && row < static_cast<int64_t>(p.rows);
-        if (VEC4) {
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (present) {
-                const uint32_t packed = reinterpret_cast<const uint32_t*>(p.values + static_cast<uint64_t>(row) * p.dim)[c];
-                const float2 mm = p.minmax[row];
-                const float range = __fsub_rn(mm.y, mm.x);
-                v.x = uniformDequant(mm.x, range, packed & 0xff, p.levels);
-                v.y = uniformDequant(mm.x, range, (packed >> 8) & 0xff, p.levels);
-                v.z = uniformDequant(mm.x, range, (packed >> 16) & 0xff, p.levels);
-                v.w = uniformDequant(mm.x, range, packed >> 24, p.levels);
+    forEachElement<FLAT_BATCH, UniformState>(
+        n, perRow,
+        [&](uint64_t i, uint32_t c) {
+            UniformState st;
+            const int64_t row = ids ? static_cast<int64_t>(__ldg(ids + i)) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
+            st.present = row >= 0 && row < static_cast<int64_t>(p.rows);
+            st.dst = o.out + i * o.rowStride + o.colOffset + (VEC4 ? 4 * c : c);
+            st.mm = make_float2(0.f, 0.f);
+            st.packed = 0;
+            if (st.present) {
+                const uint8_t* src = p.values + static_cast<uint64_t>(row) * p.dim;
+                st.packed = VEC4 ? __ldg(reinterpret_cast<const uint32_t*>(src) + c) : static_cast<uint32_t>(__ldg(src + c));
+                st.mm = __ldg(p.minmax + row);
             }
-            float4* dst = reinterpret_cast<float4*>(o.out + i * o.rowStride + o.colOffset) + c;
-            if (EPI != EPI_WRITE) {
-                const float4 old = *dst;
-                v.x = applyEpilogue(v.x, old.x, EPI, o.divisor);
-                v.y = applyEpilogue(v.y, old.y, EPI, o.divisor);
-                v.z = applyEpilogue(v.z, old.z, EPI, o.divisor);
-                v.w = applyEpilogue(v.w, old.w, EPI, o.divisor);
+            return st;
+        },
+        [&](const UniformState& st) {
+            const float range = __fsub_rn(st.mm.y, st.mm.x);
+            if (VEC4) {
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (st.present) {
+                    v.x = uniformDequant(st.mm.x, range, st.packed & 0xff, p.levels, p.invLevels, p.divMode);
+                    v.y = uniformDequant(st.mm.x, range, (st.packed >> 8) & 0xff, p.levels, p.invLevels, p.divMode);
+                    v.z = uniformDequant(st.mm.x, range, (st.packed >> 16) & 0xff, p.levels, p.invLevels, p.divMode);
+                    v.w = uniformDequant(st.mm.x, range, st.packed >> 24, p.levels, p.invLevels, p.divMode);
+                }
+                float4* dst = reinterpret_cast<float4*>(st.dst);
+                if (EPI != EPI_WRITE) {
+                    const float4 old = *dst;
+                    v.x = applyEpilogue(v.x, old.x, EPI, o.divisor);
+                    v.y = applyEpilogue(v.y, old.y, EPI, o.divisor);
+                    v.z = applyEpilogue(v.z, old.z, EPI, o.divisor);
+                    v.w = applyEpilogue(v.w, old.w, EPI, o.divisor);
+                }
+                __stcs(dst, v);
+            } else {
+                float v = st.present ? uniformDequant(st.mm.x, range, st.packed, p.levels, p.invLevels, p.divMode) : 0.f;
+                if (EPI != EPI_WRITE) {
+                    v = applyEpilogue(v, *st.dst, EPI, o.divisor);
+                }
+                __stcs(st.dst, v);
             }
-            __stcs(dst, v);
-        } else {
-            float v = 0.f;
-            if (present) {
-                const float2 mm = p.minmax[row];
-                v = uniformDequant(mm.x, __fsub_rn(mm.y, mm.x), p.values[static_cast<uint64_t>(row) * p.dim + c],
-                                   p.levels);
-            }
-            float* dst = o.out + i * o.rowStride + o.colOffset + c;
-            if (EPI != EPI_WRITE) {
-                v = applyEpilogue(v, *dst, EPI, o.divisor);
-            }
-            __stcs(dst, v);
-        }
-    }
+        });
 }
 
 // --------------------------------------------------------------- K3 full ----
@@ -1069,41 +1154,54 @@ struct FullParams {
     uint32_t dim;
 };
 
+struct FullState {
+    float* dst;
+    float4 v;  // VEC4: four values; else .x
+};
+
 template <bool VEC4, int EPI>
 __global__ void full_gather_kernel(const FullParams p, const int32_t* __restrict__ ids, uint32_t rowBegin,
                                    uint64_t n, const OutputSpec o)
 {
     const uint32_t perRow = VEC4 ? p.dim / 4 : p.dim;
-    const uint64_t total = n * perRow;
-    for (uint64_t e = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; e < total;
-         e += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
-        const uint64_t i = e / perRow;
-        const uint32_t c = static_cast<uint32_t>(e - i * perRow);
-        const int64_t row = ids ? static_cast<int64_t>(ids[i]) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
-        const bool present = row >= 0 && row < static_cast<int64_t>(p.rows);
-        if (VEC4) {
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    forEachElement<FLAT_BATCH, FullState>(
+        n, perRow,
+        [&](uint64_t i, uint32_t c) {
+            FullState st;
+            const int64_t row = ids ? static_cast<int64_t>(__ldg(ids + i)) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
+            const bool present = row >= 0 && row < static_cast<int64_t>(p.rows);
+            st.dst = o.out + i * o.rowStride + o.colOffset + (VEC4 ? 4 * c : c);
+            st.v = make_float4(0.f, 0.f, 0.f, 0.f);
             if (present) {
-                v = reinterpret_cast<const float4*>(p.values + static_cast<uint64_t>(row) * p.dim)[c];
+                const float* src = p.values + static_cast<uint64_t>(row) * p.dim;
+                if (VEC4) {
+                    st.v = __ldg(reinterpret_cast<const float4*>(src) + c);
+                } else {
+                    st.v.x = __ldg(src + c);
+                }
             }
-            float4* dst = reinterpret_cast<float4*>(o.out + i * o.rowStride + o.colOffset) + c;
-            if (EPI != EPI_WRITE) {
-                const float4 old = *dst;
-                v.x = applyEpilogue(v.x, old.x, EPI, o.divisor);
-                v.y = applyEpilogue(v.y, old.y, EPI, o.divisor);
-                v.z = applyEpilogue(v.z, old.z, EPI, o.divisor);
-                v.w = applyEpilogue(v.w, old.w, EPI, o.divisor);
+            return st;
+        },
+        [&](const FullState& st) {
+            if (VEC4) {
+                float4 v = st.v;
+                float4* dst = reinterpret_cast<float4*>(st.dst);
+                if (EPI != EPI_WRITE) {
+                    const float4 old = *dst;
+                    v.x = applyEpilogue(v.x, old.x, EPI, o.divisor);
+                    v.y = applyEpilogue(v.y, old.y, EPI, o.divisor);
+                    v.z = applyEpilogue(v.z, old.z, EPI, o.divisor);
+                    v.w = applyEpilogue(v.w, old.w, EPI, o.divisor);
+                }
+                __stcs(dst, v);
+            } else {
+                float v = st.v.x;
+                if (EPI != EPI_WRITE) {
+                    v = applyEpilogue(v, *st.dst, EPI, o.divisor);
+                }
+                __stcs(st.dst, v);
             }
-            __stcs(dst, v);
-        } else {
-            float v = present ? p.values[static_cast<uint64_t>(row) * p.dim + c] : 0.f;
-            float* dst = o.out + i * o.rowStride + o.colOffset + c;
-            if (EPI != EPI_WRITE) {
-                v = applyEpilogue(v, *dst, EPI, o.divisor);
-            }
-            __stcs(dst, v);
-        }
-    }
+        });
 }
 
 }  // namespace kernels

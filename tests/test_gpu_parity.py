@@ -188,6 +188,31 @@ def test_uniform_omitted_fields_and_odd_dim(abi, oracle, workdir):
     assert bits_equal(reader.lookup_words(words), want.batch_embedding(words))
 
 
+@pytest.mark.parametrize("levels", [2, 4, 16, 255, 3, 100, 254, 1])
+def test_uniform_divisor_modes_extreme_ranges(abi, oracle, workdir, levels):
+    """`/ levels` runs as an exact multiply (powers of two), a constant-divisor FMA sequence
+    (255) or the IEEE divide (anything else a file may hold); all must equal the reference's
+    fp32 division bit for bit, including tiny, huge, zero, negative and denormal ranges where
+    the FMA sequence has to hand over to the IEEE divide."""
+    rng = np.random.default_rng(levels)
+    rows, dim = 640, 300
+    words = [("x%03d" % i).encode() for i in rng.permutation(rows)]
+    values = rng.integers(0, 256, (rows, dim)).astype(np.uint8)
+    scale = np.float32(10.0) ** rng.integers(-44, 38, rows).astype(np.float32)
+    mins = (rng.standard_normal(rows).astype(np.float32) * scale).astype(np.float32)
+    maxs = (mins + rng.random(rows).astype(np.float32) * scale).astype(np.float32)
+    maxs[::7] = mins[::7]                      # zero range
+    maxs[3::11] = -maxs[3::11]                 # max < min: negative range (and -0 products)
+    mins[5::13] = np.float32(-0.0)
+    maxs[6::17] = np.float32(3.0e38)           # products overflow to inf
+    path = str(workdir / ("uni_div_%d.bin" % levels))
+    membfile_py.write_uniform(path, words, mins, maxs, values, levels)
+    reader, want = abi.open_checked(path), oracle.open(path)
+    with np.errstate(all="ignore"):
+        assert bits_equal(reader.lookup_words(words), want.batch_embedding(words))
+        assert bits_equal(reader.decode_range(0, rows), want.decode_range(0, rows))
+
+
 @pytest.mark.parametrize("dim", [3, 300])
 def test_full_parity(abi, oracle, synthetic, dim):
     syn = synthetic("full", 8, rows=2000, dim=dim)
