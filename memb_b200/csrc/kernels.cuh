@@ -312,9 +312,18 @@ constexpr uint32_t TRAINED_CODEBOOK_BYTES = 1024;  // 256 centroids
 constexpr uint32_t TRAINED_CHUNK = 32;             // symbols decoded between two flushes
 constexpr uint32_t TRAINED_CHUNK_UNITS = TRAINED_CHUNK / 4;       // 16 B output units (= tile words) per chunk and row
 constexpr uint32_t TRAINED_RING_UNITS = 2 * TRAINED_CHUNK_UNITS;  // the tile keeps the last two chunks of every row
-constexpr uint32_t TRAINED_TILE_STRIDE = TRAINED_RING_UNITS * 4 + 4;  // bytes per tile row: ring + 4 (bank skew)
 constexpr uint32_t TRAINED_FLUSH_ROWS = 32 / TRAINED_CHUNK_UNITS;  // rows covered by one store instruction
-constexpr uint32_t TRAINED_TILE_BYTES = 32 * TRAINED_TILE_STRIDE;
+// Symbol tile of a warp: 32 rows x ring of 16 words.  Word w of row r lives at word
+//   (r >> 2) * 65 + (w >> 3) * 32 + (r & 3) * 8 + (w & 7)
+// so that (a) the decode, where lane l writes the same word w of row l, hits bank
+// (l >> 2) + 8 * (l & 3) + (w & 7): 32 distinct banks; and (b) the flush, where 8 lanes read
+// 8 consecutive ring words of each of the rows 4*it .. 4*it+3 starting anywhere, hits
+// banks it + 8 * (r & 3) + {0..7}: 32 distinct banks whatever the rows' start offsets
+// (the skewed-stride layout of the first versions lost 13 % of its shared-memory
+// wavefronts to conflicts there, ncu r01).
+constexpr uint32_t TRAINED_TILE_GROUP_BYTES = 65 * 4;  // four rows (+ one word of skew)
+static_assert(TRAINED_CHUNK_UNITS == 8 && TRAINED_FLUSH_ROWS == 4, "tile layout is written for 32-symbol chunks");
+constexpr uint32_t TRAINED_TILE_BYTES = 17 * 128;  // 8 groups of 260 B, rounded up to 128 B
 constexpr uint32_t TRAINED_MAX_DIM = 4095;  // consumed bits live in 16 bits: dim * 16 < 65536
 constexpr uint32_t TRAINED_MAX_WARPS = 10;  // measured optimum (sweep r01: 8 -> 2.98, 10 -> 3.22, 12 -> 3.10 G rows/s) ...
 constexpr uint32_t TRAINED_MAX_REGS = 168;  // ... up to three warps on a scheduler, which owns 16384 registers: 3 x 32 x 168 = 16128
@@ -351,6 +360,16 @@ __host__ __device__ inline TrainedLayout trainedLayout(uint32_t base, uint32_t l
     l.highStart = l.lut + lutBytes;
     l.end = l.highStart + (warps - l.lowWarps) * perWarp;
     return l;
+}
+
+__device__ __forceinline__ uint32_t tileRowBase(uint32_t tile, uint32_t r)
+{
+    return tile + (r >> 2) * TRAINED_TILE_GROUP_BYTES + (r & 3u) * 32u;
+}
+// byte offset of ring word w (any integer, taken modulo the ring) within its row
+__device__ __forceinline__ uint32_t tileWordOffset(int w)
+{
+    return ((static_cast<uint32_t>(w) & 8u) << 4) + ((static_cast<uint32_t>(w) & 7u) << 2);
 }
 
 __device__ __forceinline__ uint32_t smemAddr(const void* p)
@@ -621,7 +640,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     d.lutLane = lay.lut | (p.lutReplicas == 1 ? 0u : lane * 4u);
     d.lutMask = p.lutMask;
     d.rowLane = warpBase + lane * 4;
-    const uint32_t tileLane = tile + lane * TRAINED_TILE_STRIDE;
+    const uint32_t tileLane = tileRowBase(tile, lane);
     // The flush reads ring slots it then does not store (units before the row in the
     // first chunk, units past it in the last).  With SMALLCB a symbol byte IS a shared
     // address offset, so those slots must never hold anything but multiples of 4.
@@ -769,7 +788,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         unsigned char* const rowPtr0 = outTile + fr * rowBytes;
         const uint32_t aBase = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(rowPtr0) >> 4);
         const uint32_t aStep = static_cast<uint32_t>(rowBytes >> 4) * TRAINED_FLUSH_ROWS;  // FLUSH_ROWS rows, in 16 B units
-        const uint32_t tileRows = tile + fr * TRAINED_TILE_STRIDE;
+        const uint32_t tileRows = tileRowBase(tile, fr);  // rows 4*it + fr: + it * TRAINED_TILE_GROUP_BYTES
         const bool fastFlush = VEC4 && presentMask == 0xffffffffu && (RMW ? epi != EPI_WRITE : epi == EPI_WRITE);
 
         for (uint32_t c0 = 0; c0 < dim; c0 += TRAINED_CHUNK) {
@@ -787,7 +806,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                 }
             }
             if (presentMask) {
-                uint32_t tw = tileLane + word0 * 4;
+                uint32_t tw = tileLane + (word0 >> 3) * 128;  // this chunk's half of the ring
                 if (nsym == TRAINED_CHUNK) {
                     decodeWords<TRAINED_CHUNK / 4, G, ESCAPE>(d, p, tw);
                 } else {
@@ -852,7 +871,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int a = int((aBase + it * aStep) & 7u);
                             const int j = unitsBefore - a + int(fq) + shift;
                             const int end = last ? end0 : unitsAfter - a;
-                            const uint32_t s4 = ldsU32(tileRows + it * TRAINED_FLUSH_ROWS * TRAINED_TILE_STRIDE + ((j & (TRAINED_RING_UNITS - 1)) << 2));
+                            const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
                             const float4 v = applyEpilogue4(gatherCentroids<SMALLCB>(cb, s4), old[it], epi, o.divisor);
                             stcsF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j, v);
                         }
@@ -867,7 +886,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                         for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
                             const int a = int((aBase + it * aStep) & 7u);
                             const int j = unitsBefore - a + int(fq);
-                            const uint32_t s4 = ldsU32(tileRows + it * TRAINED_FLUSH_ROWS * TRAINED_TILE_STRIDE + ((j & (TRAINED_RING_UNITS - 1)) << 2));
+                            const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
                             const float4 v = gatherCentroids<SMALLCB>(cb, s4);
                             stcsF4(reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j, v);
                         }
@@ -877,7 +896,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int a = int((aBase + it * aStep) & 7u);
                             const int j = unitsBefore - a + int(fq);
                             const int end = last ? unitsAfter : unitsAfter - a;
-                            const uint32_t s4 = ldsU32(tileRows + it * TRAINED_FLUSH_ROWS * TRAINED_TILE_STRIDE + ((j & (TRAINED_RING_UNITS - 1)) << 2));
+                            const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
                             const float4 v = gatherCentroids<SMALLCB>(cb, s4);
                             stcsF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j, v);
                         }
@@ -886,7 +905,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
                                 const int a = int((aBase + it * aStep) & 7u);
                                 const int j2 = unitsBefore - a + int(fq) + int(TRAINED_CHUNK_UNITS);
-                                const uint32_t s4 = ldsU32(tileRows + it * TRAINED_FLUSH_ROWS * TRAINED_TILE_STRIDE + ((j2 & (TRAINED_RING_UNITS - 1)) << 2));
+                                const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j2));
                                 const float4 u = gatherCentroids<SMALLCB>(cb, s4);
                                 stcsF4If(j2 < unitsAfter, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j2, u);
                             }
@@ -905,7 +924,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
                                 if (rowPresent) {
                                     v = gatherCentroids<SMALLCB>(
-                                        cb, ldsU32(tileRows + it * TRAINED_FLUSH_ROWS * TRAINED_TILE_STRIDE + ((j & (TRAINED_RING_UNITS - 1)) << 2)));
+                                        cb, ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j)));
                                 }
                                 float4* dst = reinterpret_cast<float4*>(rowPtr) + j;
                                 if (epi != EPI_WRITE) {
@@ -925,7 +944,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                 const uint32_t fieldShift = 2u - p.symShift;  // symbol field -> byte offset into the codebook
                 for (uint32_t r = 0; r < rowsHere; ++r) {
                     const bool rowPresent = (presentMask >> r) & 1u;
-                    const uint32_t tileRow = tile + r * TRAINED_TILE_STRIDE + word0 * 4;
+                    const uint32_t tileRow = tileRowBase(tile, r) + (word0 >> 3) * 128;
                     float* const dstRow = reinterpret_cast<float*>(outTile + r * rowBytes) + c0;
                     for (uint32_t c = lane; c < nsym; c += WARP) {
                         float v = 0.f;
