@@ -47,6 +47,8 @@ def parse_args():
     p.add_argument("--batch", type=int, default=1_000_000, help="row ids per step and per GPU")
     p.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (0 = auto)")
     p.add_argument("--no-extra", action="store_true", help="skip the secondary measurements")
+    p.add_argument("--ids", default="random", choices=["random", "sequential", "blocks32"],
+                   help="experiment: id distribution of the batch (the headline is `random`)")
     p.add_argument("--trained-warps", type=int, default=0, help="experiment: cap resident warps per SM (0 = auto)")
     p.add_argument("--cache-dir", default=os.environ.get("MEMB_B200_BENCH_DIR", "/tmp/memb_b200_bench"))
     return p.parse_args()
@@ -97,6 +99,11 @@ def build_table(args, storage="trained", bits=None, seed=3, rows=None):
 
 def batch_ids(args, rank):
     rng = np.random.Generator(np.random.PCG64([4, rank]))
+    if getattr(args, "ids", "random") == "sequential":
+        return (np.arange(args.batch, dtype=np.int64) % args.rows).astype(np.int32)
+    if getattr(args, "ids", "random") == "blocks32":
+        starts = rng.integers(0, args.rows // 32, (args.batch + 31) // 32, dtype=np.int64) * 32
+        return (starts[:, None] + np.arange(32)[None, :]).reshape(-1)[:args.batch].astype(np.int32)
     return rng.integers(0, args.rows, args.batch, dtype=np.int64).astype(np.int32)
 
 
@@ -508,6 +515,29 @@ def extras(args, reader, device, peak):
                                "note": "Reader.batch_embedding(list[str]) incl. Python str marshalling, H2D, resolve "
                                        "kernel, decode, D2H into a fresh numpy array"}
     del got
+    # the same words with the result left on the GPU (as_tensor=True), and pre-packed
+    # (UTF-8 blob + offsets: no Python objects per word); resolve alone = K0 + its copies
+    from memb_b200 import _memb
+    packed = _memb.pack_words(words)
+
+    def wall(fn, reps=5):
+        fn()
+        torch.cuda.synchronize()
+        best = float("inf")
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            fn()
+            torch.cuda.synchronize()
+            best = min(best, time.perf_counter() - t0)
+        return best
+
+    for name, fn in (("words_list_to_device_tensor", lambda: reader.batch_embedding(words, as_tensor=True)),
+                     ("words_packed_to_device_tensor", lambda: reader.batch_embedding(packed, as_tensor=True)),
+                     ("words_packed_to_numpy", lambda: reader.batch_embedding(packed)),
+                     ("resolve_packed_to_host_ids", lambda: reader.resolve(packed))):
+        dt = wall(fn)
+        result[name] = {"words": n, "s": dt, "rows_per_s": n / dt}
+    result["words_query_bytes"] = len(packed[0])
     return result
 
 

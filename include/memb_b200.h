@@ -99,6 +99,12 @@ memb_b200_status memb_b200_resolve(memb_b200_reader* reader, const char* query_b
  * out_host: n*dim floats, row-major. */
 memb_b200_status memb_b200_lookup_words(memb_b200_reader* reader, const char* query_bytes,
                                         const uint64_t* query_offsets, uint64_t n, float* out_host);
+/* Same lookup with the result left where the caller wants it (additive; SURVEY 8(f)-2:
+ * python/memb/reader.py:94-111 feeds a GPU embedding layer).  out: host or device memory
+ * on the reader's device; complete on return. */
+memb_b200_status memb_b200_lookup_words_to(memb_b200_reader* reader, const char* query_bytes,
+                                           const uint64_t* query_offsets, uint64_t n, float* out,
+                                           memb_b200_mem_kind out_kind);
 
 /* The decode half of extract for n row ids — src/trained_compression.cpp:129-136,
  * src/uniform_compression.cpp:58-73, src/full_compression.cpp:41-42, plus the
@@ -122,6 +128,10 @@ memb_b200_status memb_b200_decode_range(memb_b200_reader* reader, uint64_t row_b
 memb_b200_status memb_b200_union_lookup_words(memb_b200_reader* const* readers, uint32_t num_readers,
                                               memb_b200_union_mode mode, const char* query_bytes,
                                               const uint64_t* query_offsets, uint64_t n, float* out_host);
+memb_b200_status memb_b200_union_lookup_words_to(memb_b200_reader* const* readers, uint32_t num_readers,
+                                                 memb_b200_union_mode mode, const char* query_bytes,
+                                                 const uint64_t* query_offsets, uint64_t n, float* out,
+                                                 memb_b200_mem_kind out_kind);
 memb_b200_status memb_b200_union_decode_ids(memb_b200_reader* const* readers, uint32_t num_readers,
                                             memb_b200_union_mode mode, const int32_t* ids,
                                             memb_b200_mem_kind ids_kind, uint64_t n, float* out,

@@ -9,6 +9,7 @@
 #include <pybind11/stl.h>
 
 #include <cstring>
+#include <memory>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -31,34 +32,165 @@ void check(memb_b200_status status)
     throw std::runtime_error(message);
 }
 
-// list[str] -> (blob, offsets).  Python str -> UTF-8 like pybind11's
-// std::string caster used by the reference (python/memb_bindings.cpp:54-56).
+// Query words as one byte blob + n+1 offsets, the form the C ABI takes.
+// list[str]: Python str -> UTF-8 like pybind11's std::string caster used by the
+// reference (python/memb_bindings.cpp:54-56).  Additive fast paths:
+// a (blob, offsets) pair is passed through without a copy, NumPy 'S' / 'U' arrays are
+// packed without creating Python objects.
 struct Marshalled {
     std::string blob;
-    std::vector<uint64_t> offsets;
+    std::vector<uint64_t> ownedOffsets;
+    py::object keepBlob, keepOffsets;  // zero-copy sources
+    const char* data = "";
+    const uint64_t* offsets = nullptr;
+    size_t n = 0;
+
+    void adoptOwned()
+    {
+        data = blob.data();
+        offsets = ownedOffsets.data();
+        n = ownedOffsets.size() - 1;
+    }
 };
 
-Marshalled marshal(const py::list& words)
+void marshalList(const py::handle& words, Marshalled& m)
 {
-    Marshalled m;
-    const size_t n = words.size();
-    m.offsets.reserve(n + 1);
-    m.offsets.push_back(0);
-    m.blob.reserve(n * 8);
-    for (const py::handle& item : words) {
-        if (PyUnicode_Check(item.ptr())) {
+    PyObject* seq = words.ptr();
+    const Py_ssize_t n = PySequence_Fast_GET_SIZE(seq);
+    PyObject** items = PySequence_Fast_ITEMS(seq);
+    m.ownedOffsets.reserve(static_cast<size_t>(n) + 1);
+    m.ownedOffsets.push_back(0);
+    m.blob.reserve(static_cast<size_t>(n) * 8);
+    for (Py_ssize_t i = 0; i < n; ++i) {
+        PyObject* item = items[i];
+        if (PyUnicode_Check(item)) {
             Py_ssize_t size = 0;
-            const char* utf8 = PyUnicode_AsUTF8AndSize(item.ptr(), &size);
+            const char* utf8 = PyUnicode_AsUTF8AndSize(item, &size);
             if (!utf8) {
                 throw py::error_already_set();
             }
             m.blob.append(utf8, static_cast<size_t>(size));
-        } else if (PyBytes_Check(item.ptr())) {
-            m.blob.append(PyBytes_AS_STRING(item.ptr()), static_cast<size_t>(PyBytes_GET_SIZE(item.ptr())));
+        } else if (PyBytes_Check(item)) {
+            m.blob.append(PyBytes_AS_STRING(item), static_cast<size_t>(PyBytes_GET_SIZE(item)));
         } else {
             throw py::type_error("batch_embedding(): words must be str");
         }
-        m.offsets.push_back(m.blob.size());
+        m.ownedOffsets.push_back(m.blob.size());
+    }
+    m.adoptOwned();
+}
+
+void appendUtf8(std::string& out, uint32_t c)
+{
+    if (c < 0x80) {
+        out.push_back(static_cast<char>(c));
+    } else if (c < 0x800) {
+        out.push_back(static_cast<char>(0xC0 | (c >> 6)));
+        out.push_back(static_cast<char>(0x80 | (c & 0x3F)));
+    } else if (c < 0x10000) {
+        out.push_back(static_cast<char>(0xE0 | (c >> 12)));
+        out.push_back(static_cast<char>(0x80 | ((c >> 6) & 0x3F)));
+        out.push_back(static_cast<char>(0x80 | (c & 0x3F)));
+    } else {
+        out.push_back(static_cast<char>(0xF0 | (c >> 18)));
+        out.push_back(static_cast<char>(0x80 | ((c >> 12) & 0x3F)));
+        out.push_back(static_cast<char>(0x80 | ((c >> 6) & 0x3F)));
+        out.push_back(static_cast<char>(0x80 | (c & 0x3F)));
+    }
+}
+
+// 1-D NumPy array of dtype 'S<w>' (bytes, NUL padded) or 'U<w>' (UCS-4, NUL padded).
+void marshalArray(const py::array& array, Marshalled& m)
+{
+    if (array.ndim() != 1) {
+        throw py::type_error("batch_embedding(): word array must be 1-dimensional");
+    }
+    const char kind = array.dtype().kind();
+    const size_t n = static_cast<size_t>(array.shape(0));
+    const size_t item = static_cast<size_t>(array.itemsize());
+    const py::ssize_t stride = array.strides(0);
+    const char* base = static_cast<const char*>(array.data());
+    m.ownedOffsets.reserve(n + 1);
+    m.ownedOffsets.push_back(0);
+    if (kind == 'S') {
+        m.blob.reserve(n * item);
+        for (size_t i = 0; i < n; ++i) {
+            const char* p = base + static_cast<py::ssize_t>(i) * stride;
+            m.blob.append(p, strnlen(p, item));
+            m.ownedOffsets.push_back(m.blob.size());
+        }
+    } else if (kind == 'U') {
+        if (array.dtype().byteorder() == '>') {
+            throw py::type_error("batch_embedding(): big-endian unicode arrays are not supported");
+        }
+        const size_t chars = item / 4;
+        m.blob.reserve(n * chars);
+        for (size_t i = 0; i < n; ++i) {
+            const char* p = base + static_cast<py::ssize_t>(i) * stride;
+            size_t len = chars;
+            uint32_t c;
+            while (len > 0 && (std::memcpy(&c, p + (len - 1) * 4, 4), c == 0)) {
+                --len;  // NumPy strips trailing NULs only
+            }
+            for (size_t k = 0; k < len; ++k) {
+                std::memcpy(&c, p + k * 4, 4);
+                appendUtf8(m.blob, c);
+            }
+            m.ownedOffsets.push_back(m.blob.size());
+        }
+    } else {
+        throw py::type_error("batch_embedding(): word array must have dtype 'S' or 'U'");
+    }
+    m.adoptOwned();
+}
+
+// (blob, offsets): blob = any contiguous byte buffer, offsets = uint64[n+1], ascending.
+void marshalPacked(const py::tuple& packed, Marshalled& m)
+{
+    if (packed.size() != 2) {
+        throw py::type_error("batch_embedding(): packed words must be a (blob, offsets) pair");
+    }
+    py::buffer blob = packed[0].cast<py::buffer>();
+    const py::buffer_info blobInfo = blob.request();
+    auto offsets = py::array_t<uint64_t, py::array::c_style | py::array::forcecast>::ensure(packed[1]);
+    if (!offsets || offsets.ndim() != 1 || offsets.shape(0) < 1) {
+        throw py::type_error("batch_embedding(): offsets must be a 1-D uint64 array with n+1 entries");
+    }
+    const size_t blobBytes = static_cast<size_t>(blobInfo.size * blobInfo.itemsize);
+    const uint64_t* o = offsets.data();
+    const size_t n = static_cast<size_t>(offsets.shape(0)) - 1;
+    for (size_t i = 0; i < n; ++i) {
+        if (o[i] > o[i + 1]) {
+            throw py::value_error("batch_embedding(): offsets must be ascending");
+        }
+    }
+    if (o[n] > blobBytes) {
+        throw py::value_error("batch_embedding(): offsets run past the end of the blob");
+    }
+    m.keepBlob = blob;
+    m.keepOffsets = offsets;
+    m.data = static_cast<const char*>(blobInfo.ptr);
+    m.offsets = o;
+    m.n = n;
+}
+
+std::unique_ptr<Marshalled> marshal(const py::handle& words)
+{
+    auto m = std::make_unique<Marshalled>();
+    if (PyList_Check(words.ptr())) {
+        marshalList(words, *m);
+    } else if (PyTuple_Check(words.ptr())) {
+        marshalPacked(py::reinterpret_borrow<py::tuple>(words), *m);
+    } else if (py::isinstance<py::array>(words)) {
+        const py::array array = py::reinterpret_borrow<py::array>(words);
+        if (array.dtype().kind() == 'O') {
+            const py::list list = array.attr("tolist")();
+            marshalList(list, *m);
+        } else {
+            marshalArray(array, *m);
+        }
+    } else {
+        throw py::type_error("batch_embedding(): words must be a list of str");
     }
     return m;
 }
@@ -86,18 +218,33 @@ public:
         return result;
     }
 
-    py::array_t<float> batchEmbedding(const py::list& words) const
+    // words: list[str] as in the reference; additive: (blob, offsets) or a NumPy 'S'/'U' array
+    py::array_t<float> batchEmbedding(const py::object& words) const
     {
-        const Marshalled m = marshal(words);
-        const size_t n = m.offsets.size() - 1;
-        py::array_t<float> result({static_cast<py::ssize_t>(n), static_cast<py::ssize_t>(dim())});
+        const auto m = marshal(words);
+        py::array_t<float> result({static_cast<py::ssize_t>(m->n), static_cast<py::ssize_t>(dim())});
         float* out = result.mutable_data();
         {
             py::gil_scoped_release release;
-            check(memb_b200_lookup_words(impl_, m.blob.data(), m.offsets.data(), n, out));
+            check(memb_b200_lookup_words(impl_, m->data, m->offsets, m->n, out));
         }
         return result;
     }
+
+    // additive: rows written to caller memory (torch data_ptr); returns the row count
+    uint64_t batchEmbeddingInto(const py::object& words, uintptr_t out, uint64_t capacityRows, bool outOnDevice) const
+    {
+        const auto m = marshal(words);
+        if (m->n > capacityRows) {
+            throw std::invalid_argument("batch_embedding_into: output holds fewer rows than words given");
+        }
+        py::gil_scoped_release release;
+        check(memb_b200_lookup_words_to(impl_, m->data, m->offsets, m->n, reinterpret_cast<float*>(out),
+                                        outOnDevice ? MEMB_B200_DEVICE : MEMB_B200_HOST));
+        return m->n;
+    }
+
+    static uint64_t countWords(const py::object& words) { return marshal(words)->n; }
 
     std::vector<std::string> keys() const
     {
@@ -114,12 +261,15 @@ public:
     }
 
     // ---- additive ----
-    py::array_t<int32_t> resolve(const py::list& words) const
+    py::array_t<int32_t> resolve(const py::object& words) const
     {
-        const Marshalled m = marshal(words);
-        const size_t n = m.offsets.size() - 1;
-        py::array_t<int32_t> ids(static_cast<py::ssize_t>(n));
-        check(memb_b200_resolve(impl_, m.blob.data(), m.offsets.data(), n, ids.mutable_data()));
+        const auto m = marshal(words);
+        py::array_t<int32_t> ids(static_cast<py::ssize_t>(m->n));
+        int32_t* out = ids.mutable_data();
+        {
+            py::gil_scoped_release release;
+            check(memb_b200_resolve(impl_, m->data, m->offsets, m->n, out));
+        }
         return ids;
     }
 
@@ -198,26 +348,51 @@ memb_b200_union_mode parseMode(const std::string& mode)
     throw std::invalid_argument("unknown union mode " + mode);
 }
 
-py::array_t<float> unionBatchEmbedding(const std::vector<Reader*>& readers, const std::string& mode,
-                                       const py::list& words)
-{
-    const memb_b200_union_mode m = parseMode(mode);
+struct UnionHandles {
+    memb_b200_union_mode mode;
     std::vector<memb_b200_reader*> handles;
     size_t dim = 0;
+};
+
+UnionHandles unionHandles(const std::vector<Reader*>& readers, const std::string& mode)
+{
+    UnionHandles u;
+    u.mode = parseMode(mode);
     for (const Reader* r : readers) {
-        handles.push_back(r->handle());
-        dim = (m == MEMB_B200_AVERAGE) ? r->dim() : dim + r->dim();
+        u.handles.push_back(r->handle());
+        u.dim = (u.mode == MEMB_B200_AVERAGE) ? r->dim() : u.dim + r->dim();
     }
-    const Marshalled q = marshal(words);
-    const size_t n = q.offsets.size() - 1;
-    py::array_t<float> result({static_cast<py::ssize_t>(n), static_cast<py::ssize_t>(dim)});
+    return u;
+}
+
+py::array_t<float> unionBatchEmbedding(const std::vector<Reader*>& readers, const std::string& mode,
+                                       const py::object& words)
+{
+    UnionHandles u = unionHandles(readers, mode);
+    const auto q = marshal(words);
+    py::array_t<float> result({static_cast<py::ssize_t>(q->n), static_cast<py::ssize_t>(u.dim)});
     float* out = result.mutable_data();
     {
         py::gil_scoped_release release;
-        check(memb_b200_union_lookup_words(handles.data(), static_cast<uint32_t>(handles.size()), m, q.blob.data(),
-                                           q.offsets.data(), n, out));
+        check(memb_b200_union_lookup_words(u.handles.data(), static_cast<uint32_t>(u.handles.size()), u.mode, q->data,
+                                           q->offsets, q->n, out));
     }
     return result;
+}
+
+uint64_t unionBatchEmbeddingInto(const std::vector<Reader*>& readers, const std::string& mode, const py::object& words,
+                                 uintptr_t out, uint64_t capacityRows, bool outOnDevice)
+{
+    UnionHandles u = unionHandles(readers, mode);
+    const auto q = marshal(words);
+    if (q->n > capacityRows) {
+        throw std::invalid_argument("union_batch_embedding_into: output holds fewer rows than words given");
+    }
+    py::gil_scoped_release release;
+    check(memb_b200_union_lookup_words_to(u.handles.data(), static_cast<uint32_t>(u.handles.size()), u.mode, q->data,
+                                          q->offsets, q->n, reinterpret_cast<float*>(out),
+                                          outOnDevice ? MEMB_B200_DEVICE : MEMB_B200_HOST));
+    return q->n;
 }
 
 void unionDecodeIdsInto(const std::vector<Reader*>& readers, const std::string& mode, uintptr_t ids, bool idsOnDevice,
@@ -261,14 +436,14 @@ public:
         if (info.ndim != 2 || static_cast<size_t>(info.shape[0]) != words.size()) {
             throw std::runtime_error("add_words expects a (len(words), dim) float32 matrix");
         }
-        const Marshalled m = marshal(words);
+        const auto m = marshal(words);
         // a width mismatch is reported per word by the builder itself
         if (words.size() && static_cast<uint64_t>(info.shape[1]) != dim_) {
-            check(memb_b200_builder_add_word(impl_, m.blob.data(), m.offsets[1], static_cast<const float*>(info.ptr),
+            check(memb_b200_builder_add_word(impl_, m->data, m->offsets[1], static_cast<const float*>(info.ptr),
                                              static_cast<uint64_t>(info.shape[1])));
             return;
         }
-        check(memb_b200_builder_add_words(impl_, m.blob.data(), m.offsets.data(), words.size(),
+        check(memb_b200_builder_add_words(impl_, m->data, m->offsets, words.size(),
                                           static_cast<const float*>(info.ptr)));
     }
 
@@ -323,6 +498,9 @@ PYBIND11_MODULE(_memb, m)
         .def("device", &Reader::device)
         .def("resolve", &Reader::resolve)
         .def("batch_embedding_ids", &Reader::batchEmbeddingIds)
+        .def("batch_embedding_into", &Reader::batchEmbeddingInto, py::arg("words"), py::arg("out"),
+             py::arg("capacity_rows"), py::arg("out_on_device"))
+        .def_static("count_words", &Reader::countWords)
         .def("decode_range", &Reader::decodeRange)
         .def("decode_ids_into", &Reader::decodeIdsInto, py::arg("ids"), py::arg("ids_on_device"), py::arg("n"),
              py::arg("out"), py::arg("out_on_device"), py::arg("stream") = 0)
@@ -333,8 +511,17 @@ PYBIND11_MODULE(_memb, m)
     m.def("available_compression_strategies", &availableCompressionStrategies);
     // additive
     m.def("union_batch_embedding", &unionBatchEmbedding);
+    m.def("union_batch_embedding_into", &unionBatchEmbeddingInto, py::arg("readers"), py::arg("mode"), py::arg("words"),
+          py::arg("out"), py::arg("capacity_rows"), py::arg("out_on_device"));
     m.def("union_decode_ids_into", &unionDecodeIdsInto, py::arg("readers"), py::arg("mode"), py::arg("ids"),
           py::arg("ids_on_device"), py::arg("n"), py::arg("out"), py::arg("out_on_device"), py::arg("stream") = 0);
+    // the marshalled form of a word collection: (UTF-8 bytes, uint64 offsets[n+1])
+    m.def("pack_words", [](const py::object& words) {
+        const auto q = marshal(words);
+        py::array_t<uint64_t> offsets(static_cast<py::ssize_t>(q->n + 1));
+        std::memcpy(offsets.mutable_data(), q->offsets, (q->n + 1) * sizeof(uint64_t));
+        return py::make_tuple(py::bytes(q->data + q->offsets[0], q->offsets[q->n] - q->offsets[0]), offsets);
+    });
     m.def("device_count", &memb_b200_device_count);
     m.def("launch_count", &memb_b200_launch_count);
     m.def("set_option", [](const std::string& name, int64_t value) { check(memb_b200_set_option(name.c_str(), value)); });

@@ -944,8 +944,9 @@ memb_b200_status memb_b200_resolve(memb_b200_reader* reader, const char* query_b
     });
 }
 
-memb_b200_status memb_b200_lookup_words(memb_b200_reader* reader, const char* query_bytes,
-                                        const uint64_t* query_offsets, uint64_t n, float* out_host)
+memb_b200_status memb_b200_lookup_words_to(memb_b200_reader* reader, const char* query_bytes,
+                                           const uint64_t* query_offsets, uint64_t n, float* out,
+                                           memb_b200_mem_kind out_kind)
 {
     return guarded([&] {
         if (!reader) {
@@ -956,12 +957,19 @@ memb_b200_status memb_b200_lookup_words(memb_b200_reader* reader, const char* qu
         memb_b200_reader& r = *reader;
         const int32_t* dIds = resolveToDevice(r, query_bytes, query_offsets, n, r.stream);
         const uint32_t dim = r.file->dim;
-        decodeTo(r, n, dim, out_host, MEMB_B200_HOST, r.stream, [&](uint64_t first, uint64_t count, float* dOut) {
+        decodeTo(r, n, dim, out, out_kind, r.stream, [&](uint64_t first, uint64_t count, float* dOut) {
             K::OutputSpec o{dOut, dim, 0, 1.0f};
             launchDecode(r, dIds + first, 0, count, o, K::EPI_WRITE, r.stream);
         });
+        // the scratch ids/query buffers are reused by the next call: finish before returning
         CUDA_CHECK(cudaStreamSynchronize(r.stream));
     });
+}
+
+memb_b200_status memb_b200_lookup_words(memb_b200_reader* reader, const char* query_bytes,
+                                        const uint64_t* query_offsets, uint64_t n, float* out_host)
+{
+    return memb_b200_lookup_words_to(reader, query_bytes, query_offsets, n, out_host, MEMB_B200_HOST);
 }
 
 memb_b200_status memb_b200_decode_ids(memb_b200_reader* reader, const int32_t* ids, memb_b200_mem_kind ids_kind,
@@ -1048,9 +1056,10 @@ memb_b200_status memb_b200_union_decode_ids(memb_b200_reader* const* readers, ui
     });
 }
 
-memb_b200_status memb_b200_union_lookup_words(memb_b200_reader* const* readers, uint32_t num_readers,
-                                              memb_b200_union_mode mode, const char* query_bytes,
-                                              const uint64_t* query_offsets, uint64_t n, float* out_host)
+memb_b200_status memb_b200_union_lookup_words_to(memb_b200_reader* const* readers, uint32_t num_readers,
+                                                 memb_b200_union_mode mode, const char* query_bytes,
+                                                 const uint64_t* query_offsets, uint64_t n, float* out,
+                                                 memb_b200_mem_kind out_kind)
 {
     return guarded([&] {
         if (!readers) {
@@ -1077,12 +1086,20 @@ memb_b200_status memb_b200_union_lookup_words(memb_b200_reader* const* readers, 
         for (uint32_t k = 0; k < num_readers; ++k) {
             launchResolve(*readers[k], dQuery - base, dOffsets, n, dIds + k * n, r.stream);
         }
-        decodeTo(r, n, unionDim, out_host, MEMB_B200_HOST, r.stream,
+        decodeTo(r, n, unionDim, out, out_kind, r.stream,
                  [&](uint64_t first, uint64_t count, float* dOut) {
                      launchUnion(readers, num_readers, mode, dIds, n, first, count, dOut, unionDim, r.stream);
                  });
         CUDA_CHECK(cudaStreamSynchronize(r.stream));
     });
+}
+
+memb_b200_status memb_b200_union_lookup_words(memb_b200_reader* const* readers, uint32_t num_readers,
+                                              memb_b200_union_mode mode, const char* query_bytes,
+                                              const uint64_t* query_offsets, uint64_t n, float* out_host)
+{
+    return memb_b200_union_lookup_words_to(readers, num_readers, mode, query_bytes, query_offsets, n, out_host,
+                                           MEMB_B200_HOST);
 }
 
 memb_b200_status memb_b200_host_alloc(size_t bytes, void** ptr)

@@ -2,12 +2,20 @@
 
 Every lookup runs on the GPU through `_memb` (C ABI -> sm_100a kernels).
 Additive API (not in the reference): `device=` constructor keyword,
-`resolve`, `batch_embedding_ids`, `decode_range`, `load_stats`, and
-device-tensor outputs via `*_into`.
+`resolve`, `batch_embedding_ids`, `decode_range`, `load_stats`; the keyword
+`as_tensor=True` on every lookup returns a `torch.Tensor` that stays on the
+reader's GPU (the consumer is an embedding layer on that GPU),
+and `words` may also be a NumPy 'S'/'U' array or a `(blob, offsets)` pair of
+UTF-8 bytes and uint64 offsets (no per-word Python objects).
 """
 from abc import ABC, abstractmethod
 
 from . import _memb
+
+
+def _device_rows(device, rows, dim):
+    import torch
+    return torch.empty((rows, dim), dtype=torch.float32, device=torch.device('cuda', device))
 
 
 class BaseReader(ABC):
@@ -98,17 +106,23 @@ class Reader(BaseReader):
         '''List of words contained in the model (row-id order).'''
         return self._impl.keys()
 
-    def word_embedding(self, word):
+    def word_embedding(self, word, as_tensor=False):
         '''1-D float32 array for a word; zeros when the word is absent.'''
+        if as_tensor:
+            return self.batch_embedding([word], as_tensor=True)[0]
         return self._impl.word_embedding(word)
 
-    def batch_embedding(self, words):
+    def batch_embedding(self, words, as_tensor=False):
         '''2-D float32 array for a list of words; absent words give zero rows.'''
-        return self._impl.batch_embedding(words)
+        if not as_tensor:
+            return self._impl.batch_embedding(words)
+        out = _device_rows(self._impl.device(), _memb.Reader.count_words(words), self.dim)
+        self._impl.batch_embedding_into(words, out.data_ptr(), out.shape[0], True)
+        return out
 
-    def tokenizer_embedding(self, tokenizer):
+    def tokenizer_embedding(self, tokenizer, as_tensor=False):
         '''Weights of an Embedding layer for a keras Tokenizer.'''
-        return self.batch_embedding(tokenizer_word_list(tokenizer))
+        return self.batch_embedding(tokenizer_word_list(tokenizer), as_tensor=as_tensor)
 
     def _all_rows(self, words):
         # full-vocabulary decode needs no word resolution: rows 0..V-1
@@ -123,13 +137,37 @@ class Reader(BaseReader):
         '''int32 row ids (index into keys()), -1 for absent words.'''
         return self._impl.resolve(words)
 
-    def batch_embedding_ids(self, ids):
-        '''Rows for int32 row ids; negative / out-of-range ids give zero rows.'''
-        return self._impl.batch_embedding_ids(ids)
+    def batch_embedding_ids(self, ids, as_tensor=False):
+        '''Rows for int32 row ids; negative / out-of-range ids give zero rows.
+        With as_tensor=True `ids` may be a CUDA int32 tensor: nothing crosses PCIe and
+        the decode is queued on torch's current stream.'''
+        if not as_tensor:
+            return self._impl.batch_embedding_ids(ids)
+        import torch
+        device = torch.device('cuda', self._impl.device())
+        ids = torch.as_tensor(ids, dtype=torch.int32).to(device).contiguous().reshape(-1)
+        out = _device_rows(self._impl.device(), ids.numel(), self.dim)
+        with torch.cuda.device(device):
+            stream = torch.cuda.current_stream().cuda_stream
+            self._impl.decode_ids_into(ids.data_ptr(), True, ids.numel(), out.data_ptr(), True, stream)
+        ids.record_stream(torch.cuda.current_stream(device))
+        return out
 
-    def decode_range(self, begin, end):
+    def decode_range(self, begin, end, as_tensor=False):
         '''Rows [begin, end) in row-id order as a (end-begin, dim) float32 array.'''
-        return self._impl.decode_range(begin, end)
+        if not as_tensor:
+            return self._impl.decode_range(begin, end)
+        import torch
+        if not 0 <= begin <= end <= self._impl.rows():
+            raise ValueError('decode_range: rows out of range')
+        out = _device_rows(self._impl.device(), end - begin, self.dim)
+        with torch.cuda.device(out.device):
+            self._impl.decode_range_into(begin, end, out.data_ptr(), True, torch.cuda.current_stream().cuda_stream)
+        return out
+
+    def to_tensor(self):
+        '''The whole table, row-id order (= keys() order), as a CUDA tensor.'''
+        return self.decode_range(0, self._impl.rows(), as_tensor=True)
 
     def load_stats(self):
         return self._impl.load_stats()

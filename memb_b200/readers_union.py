@@ -89,21 +89,31 @@ class ReadersUnion(BaseReader):
 
         return sorted(all_keys)
 
-    def word_embedding(self, word):
+    def word_embedding(self, word, as_tensor=False):
         '''Merged vectors from all readers for a single word'''
         if self._native:
-            return self.batch_embedding([word])[0]
+            return self.batch_embedding([word], as_tensor=as_tensor)[0]
         return self._union_maker.merge([reader.word_embedding(word) for reader in self._readers])
 
-    def batch_embedding(self, words):
-        '''Merged vectors from all readers for a list of words'''
+    def batch_embedding(self, words, as_tensor=False):
+        '''Merged vectors from all readers for a list of words.
+        as_tensor=True (additive, native readers only): CUDA tensor on the readers' GPU.'''
         if self._native:
-            return _memb.union_batch_embedding(
-                [reader._impl for reader in self._readers], self._union_maker.name, words)
+            impls = [reader._impl for reader in self._readers]
+            if as_tensor:
+                import torch
+                device = torch.device('cuda', impls[0].device())
+                out = torch.empty((_memb.Reader.count_words(words), self.dim), dtype=torch.float32, device=device)
+                _memb.union_batch_embedding_into(impls, self._union_maker.name, words, out.data_ptr(),
+                                                 out.shape[0], True)
+                return out
+            return _memb.union_batch_embedding(impls, self._union_maker.name, words)
+        if as_tensor:
+            raise TypeError('as_tensor needs native Readers in the union')
         return self._union_maker.merge([reader.batch_embedding(words) for reader in self._readers])
 
-    def tokenizer_embedding(self, tokenizer):
+    def tokenizer_embedding(self, tokenizer, as_tensor=False):
         '''Merged results of tokenizer_embedding from all readers'''
         if self._native:
-            return self.batch_embedding(tokenizer_word_list(tokenizer))
+            return self.batch_embedding(tokenizer_word_list(tokenizer), as_tensor=as_tensor)
         return self._union_maker.merge([reader.tokenizer_embedding(tokenizer) for reader in self._readers])

@@ -339,3 +339,54 @@ def test_python_api(oracle, synthetic):
     assert cat.dim == 600 and bits_equal(cat[words], np.concatenate(parts, axis=-1))
     assert union.keys() == sorted(set(syn.words) | set(other.words))
     assert memb_b200._memb.launch_count() > 0
+
+
+# ---- additive word-collection forms and device-resident results ----
+def test_word_collection_forms_and_device_tensors(oracle, synthetic):
+    import torch
+    from memb_b200 import Reader, ReadersUnion, _memb
+
+    syn = synthetic("trained", 4, rows=3000, dim=300, seed=21)
+    other = synthetic("uniform", 8, rows=2500, dim=300, seed=23)
+    want, want2 = oracle.open(syn.path), oracle.open(other.path)
+    reader, reader2 = Reader(syn.path), Reader(other.path)
+    rng = np.random.default_rng(5)
+    words = queries_for(syn, rng, 700)
+    words = [w for w in words if "\0" not in w]  # NumPy 'S'/'U' arrays cannot hold an embedded NUL
+    expect = want.batch_embedding(words)
+    packed = _memb.pack_words(words)
+    for form in (np.array(words), np.array([w.encode() for w in words]), np.array(words, dtype=object), packed):
+        assert bits_equal(reader.batch_embedding(form), expect)
+        assert np.array_equal(reader.resolve(form), reader.resolve(words))
+    sliced = (packed[0], packed[1][100:201])  # offsets need not start at 0
+    assert bits_equal(reader.batch_embedding(sliced), expect[100:200])
+    with pytest.raises(ValueError):
+        reader.batch_embedding((packed[0][:10], packed[1]))
+    with pytest.raises(TypeError):
+        reader.batch_embedding(np.zeros(3))
+
+    got = reader.batch_embedding(words, as_tensor=True)
+    assert got.is_cuda and got.dtype == torch.float32 and bits_equal(got.cpu().numpy(), expect)
+    assert bits_equal(reader.batch_embedding(packed, as_tensor=True).cpu().numpy(), expect)
+    assert reader.batch_embedding([], as_tensor=True).shape == (0, 300)
+    assert bits_equal(reader.word_embedding(words[3], as_tensor=True).cpu().numpy(), expect[3])
+    ids = reader.resolve(words)
+    on_device = torch.as_tensor(ids, device="cuda")
+    assert bits_equal(reader.batch_embedding_ids(on_device, as_tensor=True).cpu().numpy(), expect)
+    assert bits_equal(reader.batch_embedding_ids(ids, as_tensor=True).cpu().numpy(), expect)
+    assert bits_equal(reader.decode_range(7, 1500, as_tensor=True).cpu().numpy(), want.decode_range(7, 1500))
+    assert bits_equal(reader.to_tensor().cpu().numpy(), want.decode_range(0, 3000))
+
+    class Tok:
+        word_index = {w: i + 1 for i, w in enumerate(syn.words[:40])}
+        num_words = None
+
+    emb = reader.tokenizer_embedding(Tok, as_tensor=True)
+    assert emb.shape == (41, 300) and bits_equal(emb[1:].cpu().numpy(), want.batch_embedding(syn.words[:40]))
+
+    parts = [expect, want2.batch_embedding(words)]
+    for mode, merged in (("average", np.mean(parts, axis=0)), ("concatenate", np.concatenate(parts, axis=-1))):
+        union = ReadersUnion([reader, reader2], mode)
+        assert bits_equal(union.batch_embedding(np.array(words)), merged)
+        got = union.batch_embedding(packed, as_tensor=True)
+        assert got.is_cuda and bits_equal(got.cpu().numpy(), merged)

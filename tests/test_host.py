@@ -231,3 +231,37 @@ def test_tokenizer_word_list():
     assert tokenizer_word_list(Tok) == ["", "a", "b", "", "", "d"]  # reader.py:100-109
     Tok.num_words = 3
     assert tokenizer_word_list(Tok) == ["", "a", "b"]
+
+
+def test_word_collections_marshal_identically():
+    """list[str] (the reference's form, python/memb_bindings.cpp:54-56) and the additive
+    NumPy / packed forms reach the C ABI as the same UTF-8 blob + offsets."""
+    from memb_b200 import _memb
+
+    words = ["a", "", "bcd", "é€", "\U0001F600x", "the", "w" * 40]
+    blob, offsets = _memb.pack_words(words)
+    assert blob == "".join(words).encode("utf-8")
+    assert offsets.dtype == np.uint64
+    assert offsets.tolist() == np.cumsum([0] + [len(w.encode("utf-8")) for w in words]).tolist()
+    forms = [np.array(words), np.array([w.encode("utf-8") for w in words]), np.array(words, dtype=object),
+             (blob, offsets), (np.frombuffer(blob, np.uint8), offsets.tolist()), np.array(words)[::-1][::-1]]
+    for form in forms:
+        b, o = _memb.pack_words(form)
+        assert b == blob and np.array_equal(o, offsets)
+    b, o = _memb.pack_words(np.array(words)[::2])  # strided view
+    assert b == "".join(words[::2]).encode("utf-8")
+    assert _memb.pack_words([b"raw", "str"])[0] == b"rawstr"
+    assert _memb.Reader.count_words(words) == len(words)
+    assert _memb.pack_words([])[1].tolist() == [0]
+    with pytest.raises(TypeError):
+        _memb.pack_words([1, 2])
+    with pytest.raises(TypeError):
+        _memb.pack_words("the")
+    with pytest.raises(TypeError):
+        _memb.pack_words(np.zeros(3))
+    with pytest.raises(TypeError):
+        _memb.pack_words(np.array([["a", "b"]]))
+    with pytest.raises(ValueError):
+        _memb.pack_words((b"abc", np.array([0, 2, 1], np.uint64)))
+    with pytest.raises(ValueError):
+        _memb.pack_words((b"abc", np.array([0, 4], np.uint64)))
