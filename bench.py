@@ -510,11 +510,18 @@ def extras(args, reader, device, peak):
     reader.batch_embedding(words[:1000])
     t0 = time.perf_counter()
     got = reader.batch_embedding(words)
-    dt = time.perf_counter() - t0
-    result["words_api_e2e"] = {"words": n, "s": dt, "rows_per_s": n / dt,
-                               "note": "Reader.batch_embedding(list[str]) incl. Python str marshalling, H2D, resolve "
-                                       "kernel, decode, D2H into a fresh numpy array"}
+    first = time.perf_counter() - t0
     del got
+    best = float("inf")
+    for _ in range(3):
+        t0 = time.perf_counter()
+        got = reader.batch_embedding(words)
+        best = min(best, time.perf_counter() - t0)
+        del got
+    result["words_api_e2e"] = {"words": n, "s": best, "rows_per_s": n / best, "first_call_s": first,
+                               "note": "Reader.batch_embedding(list[str]) -> NumPy array: str marshalling, H2D, resolve "
+                                       "kernel, decode, D2H; the first call also pins its result buffer, later calls "
+                                       "reuse it"}
     # the same words with the result left on the GPU (as_tensor=True), and pre-packed
     # (UTF-8 blob + offsets: no Python objects per word); resolve alone = K0 + its copies
     from memb_b200 import _memb

@@ -8,8 +8,12 @@
 #include <pybind11/pybind11.h>
 #include <pybind11/stl.h>
 
+#include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <memory>
+#include <mutex>
+#include <thread>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -40,6 +44,8 @@ void check(memb_b200_status status)
 struct Marshalled {
     std::string blob;
     std::vector<uint64_t> ownedOffsets;
+    std::unique_ptr<char[]> rawBlob;  // list path: filled by several threads, never zeroed
+    std::unique_ptr<uint64_t[]> rawOffsets;
     py::object keepBlob, keepOffsets;  // zero-copy sources
     const char* data = "";
     const uint64_t* offsets = nullptr;
@@ -53,31 +59,128 @@ struct Marshalled {
     }
 };
 
+// One word of a list: where its UTF-8 bytes are.  ASCII str objects and bytes expose
+// their buffer without any call into the interpreter; anything else (non-ASCII str) goes
+// through PyUnicode_AsUTF8AndSize, which may allocate and therefore needs the GIL.
+struct WordView {
+    const char* data;
+    size_t size;
+};
+
+inline bool viewWithoutInterpreter(PyObject* item, WordView& v)
+{
+    if (PyUnicode_Check(item)) {
+        if (PyUnicode_IS_COMPACT_ASCII(item)) {
+            v.data = reinterpret_cast<const char*>(PyUnicode_1BYTE_DATA(item));
+            v.size = static_cast<size_t>(PyUnicode_GET_LENGTH(item));
+            return true;
+        }
+        return false;
+    }
+    if (PyBytes_Check(item)) {
+        v.data = PyBytes_AS_STRING(item);
+        v.size = static_cast<size_t>(PyBytes_GET_SIZE(item));
+        return true;
+    }
+    return false;
+}
+
+inline void viewWithInterpreter(PyObject* item, WordView& v)
+{
+    if (!PyUnicode_Check(item)) {
+        throw py::type_error("batch_embedding(): words must be str");
+    }
+    Py_ssize_t size = 0;
+    const char* utf8 = PyUnicode_AsUTF8AndSize(item, &size);
+    if (!utf8) {
+        throw py::error_already_set();
+    }
+    v.data = utf8;
+    v.size = static_cast<size_t>(size);
+}
+
+constexpr size_t PARALLEL_MARSHAL_MIN_WORDS = 1u << 16;
+
+unsigned marshalThreads(size_t n)
+{
+    if (n < PARALLEL_MARSHAL_MIN_WORDS) {
+        return 1;
+    }
+    if (const char* forced = std::getenv("MEMB_B200_MARSHAL_THREADS")) {
+        return static_cast<unsigned>(std::max(1, std::atoi(forced)));
+    }
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    return static_cast<unsigned>(std::min<size_t>({hw, 16, n / (PARALLEL_MARSHAL_MIN_WORDS / 4)}));
+}
+
+template <class Body>
+void forRanges(size_t n, unsigned threads, Body body)
+{
+    if (threads <= 1) {
+        body(0u, size_t(0), n);
+        return;
+    }
+    std::vector<std::thread> pool;
+    const size_t per = (n + threads - 1) / threads;
+    for (unsigned t = 1; t < threads; ++t) {
+        pool.emplace_back([=] { body(t, std::min(n, t * per), std::min(n, (t + 1) * per)); });
+    }
+    body(0u, size_t(0), std::min(n, per));
+    for (std::thread& th : pool) {
+        th.join();
+    }
+}
+
+// list[str] -> blob + offsets.  The caller holds the GIL for the whole call, so no other
+// Python thread can touch the list or its items; the worker threads only READ object
+// headers and character data (no reference counts, no allocation), which is what makes
+// the two passes below safe to run on several host threads.  1 M short words: 38 ms on
+// one thread, the cost that dominated words -> device tensor.
 void marshalList(const py::handle& words, Marshalled& m)
 {
     PyObject* seq = words.ptr();
-    const Py_ssize_t n = PySequence_Fast_GET_SIZE(seq);
+    const size_t n = static_cast<size_t>(PySequence_Fast_GET_SIZE(seq));
     PyObject** items = PySequence_Fast_ITEMS(seq);
-    m.ownedOffsets.reserve(static_cast<size_t>(n) + 1);
-    m.ownedOffsets.push_back(0);
-    m.blob.reserve(static_cast<size_t>(n) * 8);
-    for (Py_ssize_t i = 0; i < n; ++i) {
-        PyObject* item = items[i];
-        if (PyUnicode_Check(item)) {
-            Py_ssize_t size = 0;
-            const char* utf8 = PyUnicode_AsUTF8AndSize(item, &size);
-            if (!utf8) {
-                throw py::error_already_set();
+    const unsigned threads = marshalThreads(n);
+    std::unique_ptr<WordView[]> views(new WordView[n]);
+    std::vector<std::vector<size_t>> slow(threads);
+    std::vector<uint64_t> rangeBytes(threads + 1, 0);
+    forRanges(n, threads, [&](unsigned t, size_t begin, size_t end) {
+        uint64_t sum = 0;
+        for (size_t i = begin; i < end; ++i) {
+            if (viewWithoutInterpreter(items[i], views[i])) {
+                sum += views[i].size;
+            } else {
+                slow[t].push_back(i);
             }
-            m.blob.append(utf8, static_cast<size_t>(size));
-        } else if (PyBytes_Check(item)) {
-            m.blob.append(PyBytes_AS_STRING(item), static_cast<size_t>(PyBytes_GET_SIZE(item)));
-        } else {
-            throw py::type_error("batch_embedding(): words must be str");
         }
-        m.ownedOffsets.push_back(m.blob.size());
+        rangeBytes[t + 1] = sum;
+    });
+    for (unsigned t = 0; t < threads; ++t) {
+        for (size_t i : slow[t]) {
+            viewWithInterpreter(items[i], views[i]);
+            rangeBytes[t + 1] += views[i].size;
+        }
     }
-    m.adoptOwned();
+    for (unsigned t = 0; t < threads; ++t) {
+        rangeBytes[t + 1] += rangeBytes[t];
+    }
+    m.rawBlob.reset(new char[rangeBytes[threads] + 1]);
+    m.rawOffsets.reset(new uint64_t[n + 1]);
+    char* blob = m.rawBlob.get();
+    uint64_t* offsets = m.rawOffsets.get();
+    forRanges(n, threads, [&](unsigned t, size_t begin, size_t end) {
+        uint64_t at = rangeBytes[t];
+        for (size_t i = begin; i < end; ++i) {
+            offsets[i] = at;
+            std::memcpy(blob + at, views[i].data, views[i].size);
+            at += views[i].size;
+        }
+    });
+    offsets[n] = rangeBytes[threads];
+    m.data = blob;
+    m.offsets = offsets;
+    m.n = n;
 }
 
 void appendUtf8(std::string& out, uint32_t c)
@@ -195,6 +298,117 @@ std::unique_ptr<Marshalled> marshal(const py::handle& words)
     return m;
 }
 
+// Results that go back to Python as NumPy arrays are DMA targets: a fresh pageable
+// array costs a page fault per 4 KB plus the driver's bounce buffer (1 M rows: 250 ms,
+// 4.8 GB/s), a pinned one runs at PCIe rate (21.5 ms).  Pinning is itself slow, so
+// buffers are recycled: the array's base object hands its buffer back when NumPy frees
+// the array.  At most `limit` bytes stay cached; 0 switches pinned results off.
+class PinnedResults {
+public:
+    static PinnedResults& instance()
+    {
+        static PinnedResults* pool = new PinnedResults;  // never destroyed: outlives CUDA teardown order
+        return *pool;
+    }
+
+    void setLimit(uint64_t bytes)
+    {
+        std::vector<Block> drop;
+        {
+            std::lock_guard<std::mutex> lock(mutex_);
+            limit_ = bytes;
+            while (cached_ > limit_ && !free_.empty()) {
+                cached_ -= free_.back().capacity;
+                drop.push_back(free_.back());
+                free_.pop_back();
+            }
+        }
+        for (const Block& b : drop) {
+            memb_b200_host_free(b.ptr);
+        }
+    }
+    uint64_t limit() const { return limit_; }
+    uint64_t cachedBytes() const { return cached_; }
+
+    py::array_t<float> make(size_t rows, size_t cols)
+    {
+        const size_t bytes = rows * cols * sizeof(float);
+        const std::vector<py::ssize_t> shape{static_cast<py::ssize_t>(rows), static_cast<py::ssize_t>(cols)};
+        if (bytes < MIN_BYTES || limit_ == 0) {
+            return py::array_t<float>(shape);
+        }
+        Block block = take(bytes);
+        if (!block.ptr) {
+            return py::array_t<float>(shape);  // no pinned memory to be had: pageable result
+        }
+        auto* owned = new Block(block);
+        py::capsule base(owned, [](void* p) {
+            Block* b = static_cast<Block*>(p);
+            PinnedResults::instance().give(*b);
+            delete b;
+        });
+        return py::array_t<float>(shape, static_cast<float*>(block.ptr), base);
+    }
+
+private:
+    struct Block {
+        void* ptr = nullptr;
+        size_t capacity = 0;
+    };
+    static constexpr size_t MIN_BYTES = size_t(1) << 20;
+    static constexpr size_t GRANULE = size_t(2) << 20;
+
+    Block take(size_t bytes)
+    {
+        {
+            std::lock_guard<std::mutex> lock(mutex_);
+            size_t best = free_.size();
+            for (size_t i = 0; i < free_.size(); ++i) {
+                // a small result must not keep a huge block alive
+                if (free_[i].capacity >= bytes && free_[i].capacity / 4 <= bytes &&
+                    (best == free_.size() || free_[i].capacity < free_[best].capacity)) {
+                    best = i;
+                }
+            }
+            if (best != free_.size()) {
+                const Block b = free_[best];
+                free_.erase(free_.begin() + static_cast<std::ptrdiff_t>(best));
+                cached_ -= b.capacity;
+                return b;
+            }
+        }
+        Block b;
+        b.capacity = (bytes + GRANULE - 1) / GRANULE * GRANULE;
+        if (memb_b200_host_alloc(b.capacity, &b.ptr) != MEMB_B200_OK) {
+            b.ptr = nullptr;
+        }
+        return b;
+    }
+
+    void give(const Block& b)
+    {
+        {
+            std::lock_guard<std::mutex> lock(mutex_);
+            if (cached_ + b.capacity <= limit_) {
+                free_.push_back(b);
+                cached_ += b.capacity;
+                return;
+            }
+        }
+        memb_b200_host_free(b.ptr);
+    }
+
+    std::mutex mutex_;
+    std::vector<Block> free_;
+    uint64_t cached_ = 0;
+    uint64_t limit_ = uint64_t(8) << 30;
+};
+
+py::array_t<float> makeResult(size_t rows, size_t cols)
+{
+    return PinnedResults::instance().make(rows, cols);
+}
+
 class Reader {
 public:
     Reader(const std::string& filename, size_t numThreads, int device)
@@ -222,7 +436,7 @@ public:
     py::array_t<float> batchEmbedding(const py::object& words) const
     {
         const auto m = marshal(words);
-        py::array_t<float> result({static_cast<py::ssize_t>(m->n), static_cast<py::ssize_t>(dim())});
+        py::array_t<float> result = makeResult(m->n, dim());
         float* out = result.mutable_data();
         {
             py::gil_scoped_release release;
@@ -276,7 +490,7 @@ public:
     py::array_t<float> batchEmbeddingIds(py::array_t<int32_t, py::array::c_style | py::array::forcecast> ids) const
     {
         const size_t n = static_cast<size_t>(ids.size());
-        py::array_t<float> result({static_cast<py::ssize_t>(n), static_cast<py::ssize_t>(dim())});
+        py::array_t<float> result = makeResult(n, dim());
         float* out = result.mutable_data();
         const int32_t* in = ids.data();
         {
@@ -291,7 +505,7 @@ public:
         if (begin > end) {
             throw std::invalid_argument("decode_range: begin > end");
         }
-        py::array_t<float> result({static_cast<py::ssize_t>(end - begin), static_cast<py::ssize_t>(dim())});
+        py::array_t<float> result = makeResult(end - begin, dim());
         float* out = result.mutable_data();
         {
             py::gil_scoped_release release;
@@ -370,7 +584,7 @@ py::array_t<float> unionBatchEmbedding(const std::vector<Reader*>& readers, cons
 {
     UnionHandles u = unionHandles(readers, mode);
     const auto q = marshal(words);
-    py::array_t<float> result({static_cast<py::ssize_t>(q->n), static_cast<py::ssize_t>(u.dim)});
+    py::array_t<float> result = makeResult(q->n, u.dim);
     float* out = result.mutable_data();
     {
         py::gil_scoped_release release;
@@ -521,6 +735,11 @@ PYBIND11_MODULE(_memb, m)
         py::array_t<uint64_t> offsets(static_cast<py::ssize_t>(q->n + 1));
         std::memcpy(offsets.mutable_data(), q->offsets, (q->n + 1) * sizeof(uint64_t));
         return py::make_tuple(py::bytes(q->data + q->offsets[0], q->offsets[q->n] - q->offsets[0]), offsets);
+    });
+    m.def("set_pinned_result_limit", [](uint64_t bytes) { PinnedResults::instance().setLimit(bytes); },
+          "bytes of pinned result buffers kept for reuse (default 8 GiB); 0 = results in pageable memory");
+    m.def("pinned_result_state", [] {
+        return py::make_tuple(PinnedResults::instance().limit(), PinnedResults::instance().cachedBytes());
     });
     m.def("device_count", &memb_b200_device_count);
     m.def("launch_count", &memb_b200_launch_count);

@@ -390,3 +390,36 @@ def test_word_collection_forms_and_device_tensors(oracle, synthetic):
         assert bits_equal(union.batch_embedding(np.array(words)), merged)
         got = union.batch_embedding(packed, as_tensor=True)
         assert got.is_cuda and bits_equal(got.cpu().numpy(), merged)
+
+
+def test_pinned_result_buffers_are_recycled_and_optional(oracle, synthetic):
+    import gc
+    from memb_b200 import Reader, _memb
+
+    syn = synthetic("trained", 4, rows=3000, dim=300, seed=21)
+    want = oracle.open(syn.path)
+    reader = Reader(syn.path)
+    ids = np.random.default_rng(9).integers(-1, 3000, 2000).astype(np.int32)  # 2.4 MB result
+    expect = want.batch_ids(ids)
+    try:
+        _memb.set_pinned_result_limit(1 << 30)
+        first = reader.batch_embedding_ids(ids)
+        assert bits_equal(first, expect) and first.flags.writeable and first.flags.c_contiguous
+        first[0, 0] = 1.0  # an ordinary array to its owner
+        kept = reader.batch_embedding_ids(ids)  # `first` still alive: must not share its buffer
+        assert kept.ctypes.data != first.ctypes.data and bits_equal(kept, expect)
+        address = first.ctypes.data
+        del first
+        gc.collect()
+        assert _memb.pinned_result_state()[1] > 0
+        again = reader.decode_range(0, 2000)
+        assert again.ctypes.data == address and bits_equal(again, want.decode_range(0, 2000))
+        assert bits_equal(kept, expect)
+        del again, kept
+        gc.collect()
+        _memb.set_pinned_result_limit(0)
+        assert _memb.pinned_result_state() == (0, 0)
+        pageable = reader.batch_embedding_ids(ids)
+        assert pageable.flags.owndata and bits_equal(pageable, expect)
+    finally:
+        _memb.set_pinned_result_limit(8 << 30)
