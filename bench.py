@@ -47,8 +47,9 @@ def parse_args():
     p.add_argument("--batch", type=int, default=1_000_000, help="row ids per step and per GPU")
     p.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (0 = auto)")
     p.add_argument("--no-extra", action="store_true", help="skip the secondary measurements")
-    p.add_argument("--ids", default="random", choices=["random", "sequential", "blocks32"],
-                   help="experiment: id distribution of the batch (the headline is `random`)")
+    p.add_argument("--ids", default="random", choices=["random", "sequential", "blocks32", "misses5"],
+                   help="experiment: id distribution of the batch (the headline is `random`; misses5 = random "
+                        "with 5 %% of the ids -1, i.e. out-of-vocabulary words)")
     p.add_argument("--trained-warps", type=int, default=0, help="experiment: cap resident warps per SM (0 = auto)")
     p.add_argument("--cache-dir", default=os.environ.get("MEMB_B200_BENCH_DIR", "/tmp/memb_b200_bench"))
     return p.parse_args()
@@ -104,7 +105,10 @@ def batch_ids(args, rank):
     if getattr(args, "ids", "random") == "blocks32":
         starts = rng.integers(0, args.rows // 32, (args.batch + 31) // 32, dtype=np.int64) * 32
         return (starts[:, None] + np.arange(32)[None, :]).reshape(-1)[:args.batch].astype(np.int32)
-    return rng.integers(0, args.rows, args.batch, dtype=np.int64).astype(np.int32)
+    ids = rng.integers(0, args.rows, args.batch, dtype=np.int64).astype(np.int32)
+    if getattr(args, "ids", "random") == "misses5":
+        ids[rng.random(args.batch) < 0.05] = -1
+    return ids
 
 
 # ------------------------------------------------------------- oracle (CPU baseline only) ----

@@ -383,6 +383,10 @@ void loadTrained(memb_b200_reader& r)
     p.symShift = symShift;
     p.codebookSize = codebookSize;
     p.rowWords = maxRowUnits * 4 + 4;
+    // slots of the 256-entry shared codebook past the last centroid hold +0.0: the row of a
+    // missing word is "decoded" to that slot (symbol fields reach 63 with symShift 2, else 255)
+    p.hasZeroSlot = codebookSize < (symShift == 2 ? 64u : 256u) ? 1u : 0u;
+    p.zeroWord = p.hasZeroSlot ? ((codebookSize << symShift) & 0xffu) * 0x01010101u : 0u;
     r.trainedEscape = escape;
     // symbols per window reload: G * maxLen <= 64 - padBits valid bits
     const uint32_t allowed = (64 - padBits) / std::max(maxLen, 1u);

@@ -306,6 +306,8 @@ struct TrainedParams {
     uint32_t symShift;      // 2 when the codebook has <= 64 entries (symbol stored as byte offset), else 0
     uint32_t codebookSize;
     uint32_t rowWords;      // words reserved per staged row (max row units * 4 + 4)
+    uint32_t hasZeroSlot;   // the shared codebook has a slot past the last centroid (it holds +0.0) ...
+    uint32_t zeroWord;      // ... and this is its symbol field, four times: what a lane WITHOUT a row writes to the tile
 };
 
 constexpr uint32_t TRAINED_CODEBOOK_BYTES = 1024;  // 256 centroids
@@ -530,7 +532,8 @@ __device__ __forceinline__ uint32_t decodeSymbol(LaneDecoder& d, const TrainedPa
 // NW words of four symbols each, fully unrolled, window re-centred every G
 // symbols; word q goes to tileWord + 4*q.
 template <int NW, int G, bool ESCAPE>
-__device__ __forceinline__ void decodeWords(LaneDecoder& d, const TrainedParams& p, uint32_t tileWord)
+__device__ __forceinline__ void decodeWords(LaneDecoder& d, const TrainedParams& p, uint32_t tileWord, uint32_t symAnd,
+                                            uint32_t symOr)
 {
 #pragma unroll
     for (int q = 0; q < NW; ++q) {
@@ -544,7 +547,7 @@ __device__ __forceinline__ void decodeWords(LaneDecoder& d, const TrainedParams&
             // byte 2 of e (the symbol field) -> byte k of acc
             acc = __byte_perm(acc, e, k == 0 ? 0x3216 : k == 1 ? 0x3260 : k == 2 ? 0x3610 : 0x6210);
         }
-        stsU32(tileWord + 4 * q, acc);
+        stsU32(tileWord + 4 * q, (acc & symAnd) | symOr);
     }
 }
 
@@ -789,7 +792,16 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         const uint32_t aBase = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(rowPtr0) >> 4);
         const uint32_t aStep = static_cast<uint32_t>(rowBytes >> 4) * TRAINED_FLUSH_ROWS;  // FLUSH_ROWS rows, in 16 B units
         const uint32_t tileRows = tileRowBase(tile, fr);  // rows 4*it + fr: + it * TRAINED_TILE_GROUP_BYTES
-        const bool fastFlush = VEC4 && presentMask == 0xffffffffu && (RMW ? epi != EPI_WRITE : epi == EPI_WRITE);
+        // A lane without a row (missing word) decodes row 0 like the others but writes the
+        // symbol of the codebook's +0.0 slot to the tile, so the straight-line flush needs no
+        // per-row predicate: only a ragged last tile (or a codebook with no free slot) takes
+        // the general path.
+        const bool zeroFill = p.hasZeroSlot && !present;
+        const uint32_t symAnd = zeroFill ? 0u : 0xffffffffu;
+        const uint32_t symOr = zeroFill ? p.zeroWord : 0u;
+        const bool fastFlush = VEC4 && rowsHere == WARP && presentMask != 0u &&
+                               (presentMask == 0xffffffffu || p.hasZeroSlot) &&
+                               (RMW ? epi != EPI_WRITE : epi == EPI_WRITE);
 
         for (uint32_t c0 = 0; c0 < dim; c0 += TRAINED_CHUNK) {
             const uint32_t nsym = min(TRAINED_CHUNK, dim - c0);
@@ -808,23 +820,23 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
             if (presentMask) {
                 uint32_t tw = tileLane + (word0 >> 3) * 128;  // this chunk's half of the ring
                 if (nsym == TRAINED_CHUNK) {
-                    decodeWords<TRAINED_CHUNK / 4, G, ESCAPE>(d, p, tw);
+                    decodeWords<TRAINED_CHUNK / 4, G, ESCAPE>(d, p, tw, symAnd, symOr);
                 } else {
                     uint32_t nw = nsym / 4;
                     if (nw & 8) {
-                        decodeWords<8, G, ESCAPE>(d, p, tw);
+                        decodeWords<8, G, ESCAPE>(d, p, tw, symAnd, symOr);
                         tw += 32;
                     }
                     if (nw & 4) {
-                        decodeWords<4, G, ESCAPE>(d, p, tw);
+                        decodeWords<4, G, ESCAPE>(d, p, tw, symAnd, symOr);
                         tw += 16;
                     }
                     if (nw & 2) {
-                        decodeWords<2, G, ESCAPE>(d, p, tw);
+                        decodeWords<2, G, ESCAPE>(d, p, tw, symAnd, symOr);
                         tw += 8;
                     }
                     if (nw & 1) {
-                        decodeWords<1, G, ESCAPE>(d, p, tw);
+                        decodeWords<1, G, ESCAPE>(d, p, tw, symAnd, symOr);
                         tw += 4;
                     }
                     const uint32_t rest = nsym & 3;
@@ -835,7 +847,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const uint32_t e = decodeSymbol<ESCAPE>(d, p);
                             acc |= ((e >> 16) & 0xffu) << (8 * k);
                         }
-                        stsU32(tw, acc);
+                        stsU32(tw, (acc & symAnd) | symOr);
                     }
                 }
             }
