@@ -267,6 +267,46 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------- B200 arm ----
+class near_gpu:
+    """While active, the process runs on the CPUs NVML names as local to the GPU, so the
+    pinned host buffers allocated inside land on that GPU's NUMA node (host-buffer copies of
+    N ranks otherwise cross the socket interconnect).  Leaves the affinity as it was."""
+
+    def __init__(self, device_index):
+        self.device_index = device_index
+        self.cpus = None
+        self.saved = None
+
+    def __enter__(self):
+        try:
+            import pynvml
+            import torch
+
+            pynvml.nvmlInit()
+            uuid = str(torch.cuda.get_device_properties(self.device_index).uuid)
+            try:
+                handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+            except Exception:
+                handle = pynvml.nvmlDeviceGetHandleByIndex(self.device_index)
+            allowed = os.sched_getaffinity(0)
+            words = (max(allowed) + 64) // 64
+            mask = pynvml.nvmlDeviceGetCpuAffinity(handle, words)
+            local = {64 * i + b for i, w in enumerate(mask) for b in range(64) if (int(w) >> b) & 1}
+            cpus = local & allowed
+            if cpus and cpus != allowed:
+                self.saved = allowed
+                os.sched_setaffinity(0, cpus)
+            self.cpus = sorted(cpus)
+        except Exception as exc:  # no NVML, no affinity call: run unbound
+            print("near_gpu: not bound (%s)" % exc, file=sys.stderr)
+        return self
+
+    def __exit__(self, *exc):
+        if self.saved is not None:
+            os.sched_setaffinity(0, self.saved)
+        return False
+
+
 def measured_peak():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -335,7 +375,8 @@ def run_b200(args):
     impl = reader._impl
     rows, dim, n = reader.rows, reader.dim, args.batch
 
-    ids_host = torch.from_numpy(batch_ids(args, rank)).pin_memory()
+    with near_gpu(local) as binding:
+        ids_host = torch.from_numpy(batch_ids(args, rank)).pin_memory()
     ids_dev = ids_host.to(device)
     out_dev = torch.empty((n, dim), dtype=torch.float32, device=device)
     stream = torch.cuda.current_stream().cuda_stream
@@ -362,7 +403,8 @@ def run_b200(args):
     value = world * n / (ms_step / 1e3)
 
     # ---- e2e: the C-ABI call with HOST buffers (pinned), H2D ids + D2H rows inside the timed region ----
-    out_host = torch.empty((n, dim), dtype=torch.float32).pin_memory()
+    with near_gpu(local):
+        out_host = torch.empty((n, dim), dtype=torch.float32).pin_memory()
     e2e_steps = args.e2e_steps or max(3, min(args.steps, 20))
 
     def step_host():
@@ -416,7 +458,9 @@ def run_b200(args):
         "output_gb_per_s": value * dim * 4 / 1e9,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 4, "d2h_bytes_per_step": n * dim * 4,
                 "ms_per_step": e2e_ms, "steps": e2e_steps,
-                "api": "memb_b200_decode_ids(host ids -> host rows) via _memb.Reader.decode_ids_into"},
+                "api": "memb_b200_decode_ids(host ids -> host rows) via _memb.Reader.decode_ids_into",
+                "host_buffers": "pinned, allocated on the GPU's NUMA node (%s local cpus of %d allowed)"
+                                % (len(binding.cpus) if binding.cpus is not None else "?", len(os.sched_getaffinity(0)))},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": roofline,

@@ -11,6 +11,22 @@
 
 constexpr int ROW_UNITS = 75;  // 1200 B
 
+// POLICY 0: st.global.cs (streaming), 1: plain st.global (write-back), 2: st.global.cg, 3: st.global.wt
+template <int POLICY>
+__device__ __forceinline__ void store16(float4* p, float4 v)
+{
+    if (POLICY == 0) {
+        __stcs(p, v);
+    } else if (POLICY == 1) {
+        *p = v;
+    } else if (POLICY == 2) {
+        __stcg(p, v);
+    } else {
+        __stwt(p, v);
+    }
+}
+
+template <int POLICY>
 __global__ void pattern(float4* out, uint64_t rows, int seg, int delay)
 {
     const uint32_t lane = threadIdx.x & 31;
@@ -28,7 +44,7 @@ __global__ void pattern(float4* out, uint64_t rows, int seg, int delay)
                 const int a = int((reinterpret_cast<uintptr_t>(row) >> 4) & 7);
                 const int j = c * seg - a + fq;
                 if (j >= 0 && j < ROW_UNITS) {
-                    __stcs(row + j, v);
+                    store16<POLICY>(row + j, v);
                 }
             }
             if (delay) {
@@ -82,9 +98,16 @@ int main()
         printf("contiguous tiles,            %2d warps/SM: %.4f ms  %.0f GB/s\n", warps, ms, gb / ms * 1e3);
         for (int seg : {8, 16, 32}) {
             for (int delay : {0, 1000, 3000}) {
-                ms = timeIt([&] { pattern<<<grid, block>>>(out, rows, seg, delay); });
+                ms = timeIt([&] { pattern<0><<<grid, block>>>(out, rows, seg, delay); });
                 printf("seg %2d lanes (%3d B runs), delay %4d, %2d warps/SM: %.4f ms  %.0f GB/s\n", seg, seg * 16, delay,
                        warps, ms, gb / ms * 1e3);
+                if (seg == 8 && delay == 1000) {
+                    const float m1 = timeIt([&] { pattern<1><<<grid, block>>>(out, rows, seg, delay); });
+                    const float m2 = timeIt([&] { pattern<2><<<grid, block>>>(out, rows, seg, delay); });
+                    const float m3 = timeIt([&] { pattern<3><<<grid, block>>>(out, rows, seg, delay); });
+                    printf("    same with st.global %.0f GB/s, st.global.cg %.0f GB/s, st.global.wt %.0f GB/s\n",
+                           gb / m1 * 1e3, gb / m2 * 1e3, gb / m3 * 1e3);
+                }
             }
         }
     }
