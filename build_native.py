@@ -57,8 +57,9 @@ def build_library(force=False):
         if not force and not _newer(headers + [src], obj):
             continue
         if src.endswith(".cu"):
+            # MEMB_B200_NVCC_DEFS: extra -D switches for kernel experiments (development aid)
             _run([_nvcc(), *NVCC_ARCH, "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC,-Wall",
-                  "-c", src, "-o", obj])
+                  *os.environ.get("MEMB_B200_NVCC_DEFS", "").split(), "-c", src, "-o", obj])
         else:
             # -ffp-contract=off: the k-means running mean and the uniform quantiser
             # must round like the reference's plain x86-64 build (no FMA)
