@@ -675,7 +675,7 @@ def extra_configs(args, reader, device, peak):
                        "roofline_frac": n * bytes_row / (ms / 1e3) / 1e9 / peak}
         del buf
     union["ids"] = "Zipf(s=1) over a permutation of the rows, PCG64 seed 8"
-    union["launches_per_call"] = 2
+    union["launches_per_call"] = {"average": 2, "concatenate": 3}  # concatenate: + the shared-sector stitch pass
     out["readers_union_2x_trained"] = union
     del second, ids, ids2
     return out

@@ -483,7 +483,7 @@ bool vec4Ok(uint32_t dim, const K::OutputSpec& o)
            reinterpret_cast<uintptr_t>(o.out) % 16 == 0;
 }
 
-template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW>
+template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW, bool SIDE = false>
 void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
                          const K::OutputSpec& o, int epi, cudaStream_t stream)
 {
@@ -498,7 +498,7 @@ void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t
     if (tiles + 4ull * grid * r.trainedWarps >= 0xffffffffull) {
         fail(MEMB_B200_ERR_ARGUMENT, "decode: too many rows in one call");
     }
-    auto kernel = K::trained_decode_kernel<G, VEC4, ESCAPE, SMALLCB, RMW>;
+    auto kernel = K::trained_decode_kernel<G, VEC4, ESCAPE, SMALLCB, RMW, SIDE>;
     CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemBytes)));
     uint32_t* counter = r.dTileCounters + (const_cast<memb_b200_reader&>(r).launchSeq++ % memb_b200_reader::TILE_COUNTERS);
     CUDA_CHECK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), stream));
@@ -515,6 +515,11 @@ void launchTrainedVec(const memb_b200_reader& r, const int32_t* ids, uint32_t ro
 {
     const bool small = r.trained.symShift == 2;
     const bool rmw = epi != K::EPI_WRITE;
+    if (!rmw && (o.sideHead || o.sideTail)) {
+        small ? launchTrainedKernel<G, true, false, true, false, true>(r, ids, rowBegin, n, o, epi, stream)
+              : launchTrainedKernel<G, true, false, false, false, true>(r, ids, rowBegin, n, o, epi, stream);
+        return;
+    }
     if (small) {
         rmw ? launchTrainedKernel<G, true, false, true, true>(r, ids, rowBegin, n, o, epi, stream)
             : launchTrainedKernel<G, true, false, true, false>(r, ids, rowBegin, n, o, epi, stream);
@@ -529,7 +534,11 @@ void launchTrainedG(const memb_b200_reader& r, const int32_t* ids, uint32_t rowB
                     const K::OutputSpec& o, int epi, cudaStream_t stream)
 {
     if (r.trainedEscape) {
-        launchTrainedKernel<3, VEC4, true, false, false>(r, ids, rowBegin, n, o, epi, stream);
+        if (VEC4 && epi == K::EPI_WRITE && (o.sideHead || o.sideTail)) {
+            launchTrainedKernel<3, VEC4, true, false, false, VEC4>(r, ids, rowBegin, n, o, epi, stream);
+        } else {
+            launchTrainedKernel<3, VEC4, true, false, false>(r, ids, rowBegin, n, o, epi, stream);
+        }
         return;
     }
     if (!VEC4) {
@@ -640,24 +649,69 @@ uint64_t rowsPerPass(uint64_t rowFloats)
 //   concatenate: reader r WRITEs its columns [sum dim_<r, sum dim_<=r)
 //   average:     reader 0 WRITEs, readers 1..R-2 ACCUMULATE, reader R-1 FINALIZEs
 // There is never a per-reader temporary.  ids: R*n reader-major (device).
+// true when this reader's launch into `o` uses a kernel that honours OutputSpec::sideHead/sideTail
+bool canRedirectUnits(const memb_b200_reader& r, const K::OutputSpec& o)
+{
+    const uint32_t dim = r.file->dim;
+    if (!vec4Ok(dim, o) || dim < 8) {
+        return false;
+    }
+    return r.file->storage != STORAGE_TRAINED || r.trainedWarps != 0;
+}
+
 void launchUnion(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_mode mode, const int32_t* dIds,
                  uint64_t idStride, uint64_t first, uint64_t n, float* dOut, uint64_t unionDim, cudaStream_t stream)
 {
+    std::vector<K::OutputSpec> specs(R);
     uint32_t col = 0;
     for (uint32_t k = 0; k < R; ++k) {
-        K::OutputSpec o;
+        K::OutputSpec& o = specs[k];
         o.out = dOut;
         o.rowStride = unionDim;
         o.divisor = static_cast<float>(R);
-        int epi = K::EPI_WRITE;
+        o.colOffset = 0;
         if (mode == MEMB_B200_CONCATENATE) {
             o.colOffset = col;
             col += readers[k]->file->dim;
-        } else {
-            o.colOffset = 0;
+        }
+    }
+    // concatenate: block boundaries in the middle of a 32 B sector (dim 300: 1200 B = 37.5
+    // sectors) are written whole by a stitch pass from two side buffers (OutputSpec::sideHead)
+    float4* side = nullptr;
+    std::vector<uint32_t> stitched;
+    if (mode == MEMB_B200_CONCATENATE && n && (unionDim * 4) % 32 == 0 &&
+        reinterpret_cast<uintptr_t>(dOut) % 32 == 0) {
+        for (uint32_t k = 0; k + 1 < R; ++k) {
+            const uint32_t boundary = specs[k + 1].colOffset;
+            if ((boundary * 4) % 32 != 0 && canRedirectUnits(*readers[k], specs[k]) &&
+                canRedirectUnits(*readers[k + 1], specs[k + 1])) {
+                stitched.push_back(k);
+            }
+        }
+        if (!stitched.empty()) {
+            CUDA_CHECK(cudaMallocAsync(reinterpret_cast<void**>(&side), stitched.size() * 2 * n * sizeof(float4), stream));
+            for (size_t b = 0; b < stitched.size(); ++b) {
+                specs[stitched[b]].sideTail = side + (2 * b) * n;
+                specs[stitched[b] + 1].sideHead = side + (2 * b + 1) * n;
+            }
+        }
+    }
+    for (uint32_t k = 0; k < R; ++k) {
+        int epi = K::EPI_WRITE;
+        if (mode != MEMB_B200_CONCATENATE) {
             epi = k == 0 ? K::EPI_WRITE : (k + 1 == R ? K::EPI_FINALIZE : K::EPI_ACCUMULATE);
         }
-        launchDecode(*readers[k], dIds + k * idStride + first, 0, n, o, epi, stream);
+        launchDecode(*readers[k], dIds + k * idStride + first, 0, n, specs[k], epi, stream);
+    }
+    for (size_t b = 0; b < stitched.size(); ++b) {
+        const unsigned grid = static_cast<unsigned>((2 * n + 255) / 256);
+        K::stitch_sectors_kernel<<<grid, 256, 0, stream>>>(side + (2 * b) * n, side + (2 * b + 1) * n, n, dOut, unionDim,
+                                                           specs[stitched[b] + 1].colOffset);
+        ++g_launches;
+        CUDA_CHECK(cudaGetLastError());
+    }
+    if (side) {
+        CUDA_CHECK(cudaFreeAsync(side, stream));
     }
 }
 
@@ -774,6 +828,20 @@ memb_b200_status memb_b200_open(const char* path, int device, unsigned num_threa
         CUDA_CHECK(cudaDeviceGetAttribute(&value, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
         reader->smemOptin = static_cast<size_t>(value);
         CUDA_CHECK(cudaStreamCreateWithFlags(&reader->stream, cudaStreamNonBlocking));
+        {
+            // stream-ordered scratch of the union stitch pass (launchUnion): let the device's
+            // default pool keep up to 256 MiB instead of returning it at every synchronisation
+            cudaMemPool_t pool = nullptr;
+            if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+                uint64_t threshold = 0;
+                cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
+                if (threshold < (uint64_t(256) << 20)) {
+                    threshold = uint64_t(256) << 20;
+                    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
+                }
+            }
+            cudaGetLastError();
+        }
 
         const auto t1 = std::chrono::steady_clock::now();
         buildVocabulary(*reader);

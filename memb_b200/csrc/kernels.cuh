@@ -36,7 +36,43 @@ struct OutputSpec {
     uint64_t rowStride;  // floats between consecutive output rows
     uint32_t colOffset;  // first column written by this reader (concatenate)
     float divisor;       // R for FINALIZE
+    // concatenate: a column block that begins or ends in the middle of a 32 B sector shares that
+    // sector with its neighbour, which another launch writes.  A half-written sector costs a
+    // read-modify-write in DRAM (scripts/partial_sector_bw.cu: 3.2 TB/s against 5.1 TB/s with
+    // whole sectors).  When set, the first / last 16 B unit of row i goes to sideHead[i] /
+    // sideTail[i] instead and stitch_sectors_kernel writes the shared sector whole.
+    float4* sideHead = nullptr;
+    float4* sideTail = nullptr;
 };
+
+// Where the 16 B unit `unit` of output row i goes (see OutputSpec::sideHead).
+__device__ __forceinline__ float4* redirectUnit(const OutputSpec& o, float4* dst, uint64_t i, uint32_t unit,
+                                                uint32_t lastUnit)
+{
+    if (o.sideHead && unit == 0) {
+        return o.sideHead + i;
+    }
+    if (o.sideTail && unit == lastUnit) {
+        return o.sideTail + i;
+    }
+    return dst;
+}
+
+// One shared sector per row and block boundary: lower half = last unit of the block on the
+// left, upper half = first unit of the block on the right; two lanes write one whole sector.
+__global__ void stitch_sectors_kernel(const float4* __restrict__ tailOfLeft, const float4* __restrict__ headOfRight,
+                                      uint64_t n, float* out, uint64_t rowStride, uint32_t boundaryColumn)
+{
+    const uint64_t e = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    const uint64_t i = e >> 1;
+    if (i >= n) {
+        return;
+    }
+    const bool upper = e & 1;
+    const float4 v = upper ? headOfRight[i] : tailOfLeft[i];
+    float4* dst = reinterpret_cast<float4*>(out + i * rowStride + boundaryColumn) + (upper ? 0 : -1);
+    __stcs(dst, v);
+}
 
 // ------------------------------------------------------------------ hash ----
 __device__ __forceinline__ uint64_t mix64(uint64_t h)
@@ -596,7 +632,8 @@ __device__ __forceinline__ uint32_t shflFrom(uint32_t v, uint32_t srcLane)
 // SMALLCB: symShift == 2 (see gatherCentroids).
 // RMW: the launch carries an average epilogue (ACCUMULATE / FINALIZE): the fast flush
 // reads the running sum, adds, divides for the last reader, and stores.
-template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW>
+// SIDE: the launch redirects first / last units to side buffers (OutputSpec::sideHead).
+template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW, bool SIDE>
 __global__ void __maxnreg__(TRAINED_MAX_REGS)
 trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, uint32_t rowBegin, uint64_t n,
                       const OutputSpec o, const int epi, uint32_t* __restrict__ tileCounter)
@@ -910,7 +947,11 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int end = last ? unitsAfter : unitsAfter - a;
                             const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
                             const float4 v = gatherCentroids<SMALLCB>(cb, s4);
-                            stcsF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j, v);
+                            float4* dst = reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j;
+                            if (SIDE) {
+                                dst = redirectUnit(o, dst, row0 + it * TRAINED_FLUSH_ROWS + fr, static_cast<uint32_t>(j), dim / 4 - 1);
+                            }
+                            stcsF4If(j >= 0 && j < end, dst, v);
                         }
                         if (last) {
 #pragma unroll
@@ -919,7 +960,11 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                                 const int j2 = unitsBefore - a + int(fq) + int(TRAINED_CHUNK_UNITS);
                                 const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j2));
                                 const float4 u = gatherCentroids<SMALLCB>(cb, s4);
-                                stcsF4If(j2 < unitsAfter, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j2, u);
+                                float4* dst = reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j2;
+                                if (SIDE) {
+                                    dst = redirectUnit(o, dst, row0 + it * TRAINED_FLUSH_ROWS + fr, static_cast<uint32_t>(j2), dim / 4 - 1);
+                                }
+                                stcsF4If(j2 < unitsAfter, dst, u);
                             }
                         }
                     }
@@ -939,6 +984,9 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                                         cb, ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j)));
                                 }
                                 float4* dst = reinterpret_cast<float4*>(rowPtr) + j;
+                                if (SIDE) {
+                                    dst = redirectUnit(o, dst, row0 + r, static_cast<uint32_t>(j), dim / 4 - 1);
+                                }
                                 if (epi != EPI_WRITE) {
                                     const float4 old = *dst;
                                     v.x = applyEpilogue(v.x, old.x, epi, o.divisor);
@@ -1140,6 +1188,9 @@ __global__ void uniform_decode_kernel(const UniformParams p, const int32_t* __re
             const int64_t row = ids ? static_cast<int64_t>(__ldg(ids + i)) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
             st.present = row >= 0 && row < static_cast<int64_t>(p.rows);
             st.dst = o.out + i * o.rowStride + o.colOffset + (VEC4 ? 4 * c : c);
+            if (VEC4) {
+                st.dst = reinterpret_cast<float*>(redirectUnit(o, reinterpret_cast<float4*>(st.dst), i, c, perRow - 1));
+            }
             st.mm = make_float2(0.f, 0.f);
             st.packed = 0;
             if (st.present) {
@@ -1202,6 +1253,9 @@ __global__ void full_gather_kernel(const FullParams p, const int32_t* __restrict
             const int64_t row = ids ? static_cast<int64_t>(__ldg(ids + i)) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
             const bool present = row >= 0 && row < static_cast<int64_t>(p.rows);
             st.dst = o.out + i * o.rowStride + o.colOffset + (VEC4 ? 4 * c : c);
+            if (VEC4) {
+                st.dst = reinterpret_cast<float*>(redirectUnit(o, reinterpret_cast<float4*>(st.dst), i, c, perRow - 1));
+            }
             st.v = make_float4(0.f, 0.f, 0.f, 0.f);
             if (present) {
                 const float* src = p.values + static_cast<uint64_t>(row) * p.dim;

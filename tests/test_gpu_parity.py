@@ -423,3 +423,22 @@ def test_pinned_result_buffers_are_recycled_and_optional(oracle, synthetic):
         assert pageable.flags.owndata and bits_equal(pageable, expect)
     finally:
         _memb.set_pinned_result_limit(8 << 30)
+
+
+@pytest.mark.parametrize("n", [1, 31, 33, 1000])
+def test_union_concatenate_shared_sectors(abi, oracle, synthetic, n):
+    """Column blocks that begin / end in the middle of a 32 B sector (dims 12, 20, 300): the
+    shared sectors are written by the stitch pass from the readers' side buffers."""
+    syns = [synthetic("trained", 4, rows=900, dim=12, seed=41), synthetic("uniform", 8, rows=800, dim=20, seed=42),
+            synthetic("full", 4, rows=700, dim=300, seed=43), synthetic("trained", 2, rows=600, dim=300, seed=44),
+            synthetic("trained", 6, rows=500, dim=8, seed=45)]
+    readers = [abi.open_checked(s.path) for s in syns]
+    oracles = [oracle.open(s.path) for s in syns]
+    rng = np.random.default_rng(n)
+    words = sum([queries_for(s, rng, max(1, n // 5 + 1)) for s in syns], [])[:n]
+    assert len(words) == n
+    want = np.concatenate([o.batch_embedding(words) for o in oracles], axis=-1)
+    assert want.shape == (n, 640)  # 2560 B rows: boundaries at 48, 128, 1328, 2528 B
+    assert bits_equal(helpers.union_lookup_words(abi, readers, abi.CONCATENATE, words, 640), want)
+    ids = np.stack([o.resolve(words) for o in oracles])
+    assert bits_equal(helpers.union_decode_ids(abi, readers, abi.CONCATENATE, ids, 640), want)
