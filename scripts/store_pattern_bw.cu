@@ -9,7 +9,10 @@
 #include <cstdio>
 #include <cuda_runtime.h>
 
-constexpr int ROW_UNITS = 75;  // 1200 B
+#ifndef ROW_UNITS_DEF
+#define ROW_UNITS_DEF 75
+#endif
+constexpr int ROW_UNITS = ROW_UNITS_DEF;  // 75: 1200 B
 
 // POLICY 0: st.global.cs (streaming), 1: plain st.global (write-back), 2: st.global.cg, 3: st.global.wt
 template <int POLICY>

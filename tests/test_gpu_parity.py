@@ -92,7 +92,7 @@ def test_trained_parity_bits_sweep(abi, oracle, synthetic, bits):
     assert stats.codebook_size == len(want.codebook()) and stats.max_code_len == want.prefix_code()[2].max()
 
 
-@pytest.mark.parametrize("dim", [1, 3, 4, 31, 32, 33, 64, 100, 301, 768])
+@pytest.mark.parametrize("dim", [1, 3, 4, 12, 20, 31, 32, 33, 36, 44, 64, 100, 301, 768])
 def test_trained_parity_dims(abi, oracle, synthetic, dim):
     syn = synthetic("trained", 4, rows=700, dim=dim, seed=dim)
     reader, want = abi.open_checked(syn.path), oracle.open(syn.path)
