@@ -595,7 +595,9 @@ void launchDecode(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBeg
         break;
     case STORAGE_UNIFORM: {
         auto go = [&](auto kernel) { kernel<<<flatGrid, 256, 0, stream>>>(r.uniform, ids, rowBegin, n, o); };
-        if (vec) {
+        if (vec && epi == K::EPI_WRITE && (o.sideHead || o.sideTail)) {
+            go(K::uniform_decode_kernel<true, K::EPI_WRITE, true>);
+        } else if (vec) {
             epi == K::EPI_WRITE        ? go(K::uniform_decode_kernel<true, K::EPI_WRITE>)
             : epi == K::EPI_ACCUMULATE ? go(K::uniform_decode_kernel<true, K::EPI_ACCUMULATE>)
                                        : go(K::uniform_decode_kernel<true, K::EPI_FINALIZE>);
@@ -608,7 +610,9 @@ void launchDecode(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBeg
     }
     default: {
         auto go = [&](auto kernel) { kernel<<<flatGrid, 256, 0, stream>>>(r.full, ids, rowBegin, n, o); };
-        if (vec) {
+        if (vec && epi == K::EPI_WRITE && (o.sideHead || o.sideTail)) {
+            go(K::full_gather_kernel<true, K::EPI_WRITE, true>);
+        } else if (vec) {
             epi == K::EPI_WRITE        ? go(K::full_gather_kernel<true, K::EPI_WRITE>)
             : epi == K::EPI_ACCUMULATE ? go(K::full_gather_kernel<true, K::EPI_ACCUMULATE>)
                                        : go(K::full_gather_kernel<true, K::EPI_FINALIZE>);

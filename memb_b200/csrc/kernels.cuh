@@ -1176,7 +1176,7 @@ struct UniformState {
     bool present;
 };
 
-template <bool VEC4, int EPI>
+template <bool VEC4, int EPI, bool SIDE = false>
 __global__ void uniform_decode_kernel(const UniformParams p, const int32_t* __restrict__ ids, uint32_t rowBegin,
                                       uint64_t n, const OutputSpec o)
 {
@@ -1188,7 +1188,7 @@ __global__ void uniform_decode_kernel(const UniformParams p, const int32_t* __re
             const int64_t row = ids ? static_cast<int64_t>(__ldg(ids + i)) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
             st.present = row >= 0 && row < static_cast<int64_t>(p.rows);
             st.dst = o.out + i * o.rowStride + o.colOffset + (VEC4 ? 4 * c : c);
-            if (VEC4) {
+            if (VEC4 && SIDE) {
                 st.dst = reinterpret_cast<float*>(redirectUnit(o, reinterpret_cast<float4*>(st.dst), i, c, perRow - 1));
             }
             st.mm = make_float2(0.f, 0.f);
@@ -1241,7 +1241,7 @@ struct FullState {
     float4 v;  // VEC4: four values; else .x
 };
 
-template <bool VEC4, int EPI>
+template <bool VEC4, int EPI, bool SIDE = false>
 __global__ void full_gather_kernel(const FullParams p, const int32_t* __restrict__ ids, uint32_t rowBegin,
                                    uint64_t n, const OutputSpec o)
 {
@@ -1253,7 +1253,7 @@ __global__ void full_gather_kernel(const FullParams p, const int32_t* __restrict
             const int64_t row = ids ? static_cast<int64_t>(__ldg(ids + i)) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
             const bool present = row >= 0 && row < static_cast<int64_t>(p.rows);
             st.dst = o.out + i * o.rowStride + o.colOffset + (VEC4 ? 4 * c : c);
-            if (VEC4) {
+            if (VEC4 && SIDE) {
                 st.dst = reinterpret_cast<float*>(redirectUnit(o, reinterpret_cast<float4*>(st.dst), i, c, perRow - 1));
             }
             st.v = make_float4(0.f, 0.f, 0.f, 0.f);
