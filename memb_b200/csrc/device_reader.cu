@@ -336,7 +336,7 @@ void loadTrained(memb_b200_reader& r)
     for (uint32_t i = 0; i < rows; ++i) {
         rowOff16[i] = static_cast<uint32_t>(units);
         // padBits (< 8) extra bits in front of the row: one more byte
-        const uint32_t rowUnits = rowBytes[i] ? (rowBytes[i] + 1 + 15) / 16 : 0;
+        const uint32_t rowUnits = rowBytes[i] ? (rowBytes[i] + 1 + K::TRAINED_UNIT_BYTES - 1) / K::TRAINED_UNIT_BYTES : 0;
         units += rowUnits;
         payload += rowBytes[i];
         maxRowUnits = std::max(maxRowUnits, rowUnits);
@@ -348,13 +348,14 @@ void loadTrained(memb_b200_reader& r)
     r.stats.payload_bytes = payload;
     uint32_t* dRowOff16 = deviceUpload(rowOff16.data(), rowOff16.size(), r.stats.device_bytes);
     r.owned.push_back(dRowOff16);
-    uint4* dBlob = nullptr;
+    K::RowUnit* dBlob = nullptr;
     // one spare unit so the decoder's 96-bit window never leaves the allocation
-    const size_t blobBytes = (units + 1) * 16;
+    const size_t blobBytes = (units + 1) * K::TRAINED_UNIT_BYTES;
     CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&dBlob), blobBytes));
     r.stats.device_bytes += blobBytes;
     r.owned.push_back(dBlob);
-    CUDA_CHECK(cudaMemsetAsync(reinterpret_cast<unsigned char*>(dBlob) + units * 16, 0, 16, r.stream));
+    CUDA_CHECK(cudaMemsetAsync(reinterpret_cast<unsigned char*>(dBlob) + units * K::TRAINED_UNIT_BYTES, 0,
+                               K::TRAINED_UNIT_BYTES, r.stream));
     if (rows) {
         const uint64_t threads = uint64_t(rows) * 32;
         K::repack_rows_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, r.stream>>>(
@@ -382,7 +383,7 @@ void loadTrained(memb_b200_reader& r)
     p.lutMask = ((1u << lutBits) - 1) << padBits;
     p.symShift = symShift;
     p.codebookSize = codebookSize;
-    p.rowWords = maxRowUnits * 4 + 4;
+    p.rowWords = maxRowUnits * K::TRAINED_UNIT_WORDS + 4;
     // slots of the 256-entry shared codebook past the last centroid hold +0.0: the row of a
     // missing word is "decoded" to that slot (symbol fields reach 63 with symShift 2, else 255)
     p.hasZeroSlot = codebookSize < (symShift == 2 ? 64u : 256u) ? 1u : 0u;

@@ -29,6 +29,17 @@ constexpr int WARP = 32;
 //   FINALIZE    out = (out + v) / R             (average, last reader)
 // np.mean(axis=0) on fp32 is a sequential fp32 add over the readers followed by
 // one fp32 divide; __fadd_rn/__fdiv_rn keep nvcc from contracting.
+#ifndef MEMB_UNIT_BYTES
+#define MEMB_UNIT_BYTES 16
+#endif
+// A re-packed row is a whole number of units; one unit = one global load of a lane.
+constexpr uint32_t TRAINED_UNIT_BYTES = MEMB_UNIT_BYTES;  // 16: 128-bit loads, 32: 256-bit loads (one sector)
+constexpr uint32_t TRAINED_UNIT_WORDS = TRAINED_UNIT_BYTES / 4;
+static_assert(TRAINED_UNIT_BYTES == 16 || TRAINED_UNIT_BYTES == 32, "row unit is one 128- or 256-bit load");
+struct alignas(TRAINED_UNIT_BYTES) RowUnit {
+    uint32_t w[TRAINED_UNIT_WORDS];
+};
+
 enum Epilogue : int { EPI_WRITE = 0, EPI_ACCUMULATE = 1, EPI_FINALIZE = 2 };
 
 struct OutputSpec {
@@ -255,8 +266,8 @@ __global__ void repack_rows_kernel(const uint8_t* __restrict__ packed, uint64_t 
     }
     const uint64_t src = valueOffsets[warp];
     const uint32_t bytes = rowBytes[warp];
-    const uint32_t words = (rowOff16[warp + 1] - rowOff16[warp]) * 4;
-    uint32_t* dst = blob + static_cast<uint64_t>(rowOff16[warp]) * 4;
+    const uint32_t words = (rowOff16[warp + 1] - rowOff16[warp]) * TRAINED_UNIT_WORDS;
+    uint32_t* dst = blob + static_cast<uint64_t>(rowOff16[warp]) * TRAINED_UNIT_WORDS;
     // big-endian word `wi` of the row as stored in the file (zero outside the row)
     auto fileWord = [&](int64_t wi) -> uint32_t {
         uint32_t v = 0;
@@ -328,8 +339,8 @@ __global__ void pad_rows16_kernel(const uint32_t* __restrict__ rowBytes, uint32_
 // per-symbol chain carries no float and every global store is a 128-bit
 // streaming store covering 128 contiguous bytes per 8 lanes.
 struct TrainedParams {
-    const uint4* blob;
-    const uint32_t* rowOff16;
+    const RowUnit* blob;
+    const uint32_t* rowOff16;   // (name from the 16 B layout) rows+1 offsets into blob in UNITS
     const uint32_t* lut;
     const float* codebook;
     const CanonicalCode* code;
@@ -365,7 +376,7 @@ constexpr uint32_t TRAINED_TILE_BYTES = 17 * 128;  // 8 groups of 260 B, rounded
 constexpr uint32_t TRAINED_MAX_DIM = 4095;  // consumed bits live in 16 bits: dim * 16 < 65536
 constexpr uint32_t TRAINED_MAX_WARPS = 10;  // measured optimum (sweep r01: 8 -> 2.98, 10 -> 3.22, 12 -> 3.10 G rows/s) ...
 constexpr uint32_t TRAINED_MAX_REGS = 168;  // ... up to three warps on a scheduler, which owns 16384 registers: 3 x 32 x 168 = 16128
-constexpr uint32_t TRAINED_PREFETCH_UNITS = 12;  // 192 B of the next row per lane held in registers
+constexpr uint32_t TRAINED_PREFETCH_UNITS = 192 / MEMB_UNIT_BYTES;  // 192 B of the next row per lane held in registers
 
 __host__ __device__ inline uint32_t trainedLutBytes(uint32_t lutBits, uint32_t replicas)
 {
@@ -612,11 +623,28 @@ __device__ __forceinline__ float4 applyEpilogue4(float4 v, float4 old, int epi, 
     return v;
 }
 
-__device__ __forceinline__ uint4 loadRowUnit(const uint4* p)
+__device__ __forceinline__ RowUnit loadRowUnit(const RowUnit* p)
 {
-    uint4 v;
-    asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    RowUnit v;
+    if (TRAINED_UNIT_WORDS == 8) {
+        asm volatile("ld.global.nc.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                     : "=r"(v.w[0]), "=r"(v.w[1]), "=r"(v.w[2]), "=r"(v.w[3]), "=r"(v.w[4 % TRAINED_UNIT_WORDS]),
+                       "=r"(v.w[5 % TRAINED_UNIT_WORDS]), "=r"(v.w[6 % TRAINED_UNIT_WORDS]), "=r"(v.w[7 % TRAINED_UNIT_WORDS])
+                     : "l"(p));
+    } else {
+        asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(v.w[0]), "=r"(v.w[1]), "=r"(v.w[2]), "=r"(v.w[3])
+                     : "l"(p));
+    }
     return v;
+}
+// scatter a unit down the lane's own bank: word w of the unit to addr + w * 128
+__device__ __forceinline__ void stageRowUnit(uint32_t addr, const RowUnit& v)
+{
+#pragma unroll
+    for (uint32_t w = 0; w < TRAINED_UNIT_WORDS; ++w) {
+        stsU32(addr + w * 128, v.w[w]);
+    }
 }
 
 __device__ __forceinline__ uint32_t shflFrom(uint32_t v, uint32_t srcLane)
@@ -727,9 +755,9 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         }
         return ok;
     };
-    uint4 pre[TRAINED_PREFETCH_UNITS];
+    RowUnit pre[TRAINED_PREFETCH_UNITS];
     auto prefetchRows = [&](uint32_t rowO16, uint32_t rowUnits) {
-        const uint4* src = p.blob + rowO16;
+        const RowUnit* src = p.blob + rowO16;
 #pragma unroll
         for (uint32_t k = 0; k < TRAINED_PREFETCH_UNITS; ++k) {
             if (k < rowUnits) {
@@ -779,19 +807,15 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
 #pragma unroll
         for (uint32_t k = 0; k < TRAINED_PREFETCH_UNITS; ++k) {
             if (k < units) {
-                const uint32_t a = d.rowLane + k * 512;
-                stsU32(a, pre[k].x);
-                stsU32(a + 128, pre[k].y);
-                stsU32(a + 256, pre[k].z);
-                stsU32(a + 384, pre[k].w);
+                stageRowUnit(d.rowLane + k * (TRAINED_UNIT_WORDS * 128), pre[k]);
             }
         }
         {
             // rows longer than the prefetch window: the rest comes straight from HBM
-            const uint4* src = p.blob + o16;
+            const RowUnit* src = p.blob + o16;
             const uint32_t unitsMax = __reduce_max_sync(0xffffffffu, presentMask ? units : 0u);
             for (uint32_t j = TRAINED_PREFETCH_UNITS; j < unitsMax; j += 4) {
-                uint4 c[4];
+                RowUnit c[4];
 #pragma unroll
                 for (uint32_t k = 0; k < 4; ++k) {
                     if (j + k < units) {
@@ -801,11 +825,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
 #pragma unroll
                 for (uint32_t k = 0; k < 4; ++k) {
                     if (j + k < units) {
-                        const uint32_t a = d.rowLane + (j + k) * 512;
-                        stsU32(a, c[k].x);
-                        stsU32(a + 128, c[k].y);
-                        stsU32(a + 256, c[k].z);
-                        stsU32(a + 384, c[k].w);
+                        stageRowUnit(d.rowLane + (j + k) * (TRAINED_UNIT_WORDS * 128), c[k]);
                     }
                 }
             }
@@ -1050,7 +1070,7 @@ __global__ void trained_decode_generic_kernel(const TrainedParams p, const int32
     float* dst = o.out + i * o.rowStride + o.colOffset;
     const uint32_t* words = present ? reinterpret_cast<const uint32_t*>(p.blob + p.rowOff16[row]) : nullptr;
     const uint64_t limitWords =
-        present ? static_cast<uint64_t>(p.rowOff16[row + 1] - p.rowOff16[row]) * 4 : 0;
+        present ? static_cast<uint64_t>(p.rowOff16[row + 1] - p.rowOff16[row]) * TRAINED_UNIT_WORDS : 0;
     uint64_t bit = 0;
     for (uint32_t c = 0; c < p.dim; ++c) {
         float v = 0.f;
