@@ -442,3 +442,56 @@ def test_union_concatenate_shared_sectors(abi, oracle, synthetic, n):
     assert bits_equal(helpers.union_lookup_words(abi, readers, abi.CONCATENATE, words, 640), want)
     ids = np.stack([o.resolve(words) for o in oracles])
     assert bits_equal(helpers.union_decode_ids(abi, readers, abi.CONCATENATE, ids, 640), want)
+
+
+def test_concurrent_calls_on_one_reader(oracle, synthetic):
+    """memb::Reader is const and re-entrant (src/reader.h:11-40, per-call DecodeState in
+    huffman_table_decoder.h:96-100): host-buffer calls from several Python threads (the GIL is
+    released inside the binding) and device-pointer calls on several CUDA streams must all give
+    the oracle's rows."""
+    import threading
+    import torch
+    from memb_b200 import Reader, ReadersUnion
+
+    syn = synthetic("trained", 4, rows=3000, dim=300, seed=21)
+    other = synthetic("trained", 6, rows=2500, dim=300, seed=22)
+    want, want2 = oracle.open(syn.path), oracle.open(other.path)
+    reader, reader2 = Reader(syn.path), Reader(other.path)
+    union = ReadersUnion([reader, reader2], "concatenate")
+    keys = reader.keys()  # row id -> word
+    failures = []
+
+    def worker(seed):
+        try:
+            rng = np.random.default_rng(seed)
+            stream = torch.cuda.Stream()
+            for it in range(6):
+                n = int(rng.integers(1, 4000))
+                ids = rng.integers(-1, 3000, n).astype(np.int32)
+                expect = want.batch_ids(ids)
+                kind = (seed + it) % 4
+                if kind == 0:
+                    got = reader.batch_embedding_ids(ids)
+                elif kind == 1:
+                    with torch.cuda.stream(stream):
+                        got = reader.batch_embedding_ids(torch.from_numpy(ids).cuda(), as_tensor=True)
+                    stream.synchronize()
+                    got = got.cpu().numpy()
+                elif kind == 2:
+                    words = [keys[i] if i >= 0 else "missing word" for i in ids]
+                    got = reader.batch_embedding(words)
+                else:
+                    words = [keys[i] if i >= 0 else "missing word" for i in ids]
+                    got = union.batch_embedding(words)
+                    expect = np.concatenate([expect, want2.batch_embedding(words)], axis=-1)
+                if not bits_equal(got, expect):
+                    failures.append((seed, it, kind))
+        except Exception as exc:  # surfaced below: an exception in a thread would otherwise pass silently
+            failures.append((seed, repr(exc)))
+
+    threads = [threading.Thread(target=worker, args=(s,)) for s in range(8)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not failures, failures
