@@ -598,6 +598,10 @@ void launchDecode(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBeg
         auto go = [&](auto kernel) { kernel<<<flatGrid, 256, 0, stream>>>(r.uniform, ids, rowBegin, n, o); };
         if (vec && epi == K::EPI_WRITE && (o.sideHead || o.sideTail)) {
             go(K::uniform_decode_kernel<true, K::EPI_WRITE, true>);
+        } else if (vec && epi == K::EPI_WRITE) {
+            r.uniform.divMode == 1   ? go(K::uniform_decode_kernel<true, K::EPI_WRITE, false, 1>)
+            : r.uniform.divMode == 2 ? go(K::uniform_decode_kernel<true, K::EPI_WRITE, false, 2>)
+                                     : go(K::uniform_decode_kernel<true, K::EPI_WRITE, false, 0>);
         } else if (vec) {
             epi == K::EPI_WRITE        ? go(K::uniform_decode_kernel<true, K::EPI_WRITE>)
             : epi == K::EPI_ACCUMULATE ? go(K::uniform_decode_kernel<true, K::EPI_ACCUMULATE>)

@@ -1196,10 +1196,13 @@ struct UniformState {
     bool present;
 };
 
-template <bool VEC4, int EPI, bool SIDE = false>
+// DIV >= 0: the division mode (UniformParams::divMode) as a compile-time constant for the
+// plain lookup; -1: read it from the parameters.
+template <bool VEC4, int EPI, bool SIDE = false, int DIV = -1>
 __global__ void uniform_decode_kernel(const UniformParams p, const int32_t* __restrict__ ids, uint32_t rowBegin,
                                       uint64_t n, const OutputSpec o)
 {
+    const int divMode = DIV >= 0 ? DIV : p.divMode;
     const uint32_t perRow = VEC4 ? p.dim / 4 : p.dim;
     forEachElement<FLAT_BATCH, UniformState>(
         n, perRow,
@@ -1224,11 +1227,33 @@ __global__ void uniform_decode_kernel(const UniformParams p, const int32_t* __re
             const float range = __fsub_rn(st.mm.y, st.mm.x);
             if (VEC4) {
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (st.present) {
-                    v.x = uniformDequant(st.mm.x, range, st.packed & 0xff, p.levels, p.invLevels, p.divMode);
-                    v.y = uniformDequant(st.mm.x, range, (st.packed >> 8) & 0xff, p.levels, p.invLevels, p.divMode);
-                    v.z = uniformDequant(st.mm.x, range, (st.packed >> 16) & 0xff, p.levels, p.invLevels, p.divMode);
-                    v.w = uniformDequant(st.mm.x, range, st.packed >> 24, p.levels, p.invLevels, p.divMode);
+                // levels == 255: the constant-divisor sequence is verified for x = +0 and
+                // 1e-20 < |x| < 1e20 (divideByLevels).  x = RN(range * k), k = 0..255, stays inside
+                // that set for the whole row when range is +0 or 1e-20 < range < 1e20 / 256
+                // (rounding is monotone: range <= x <= RN(255 * range) < 1e20 for k >= 1, +0 for
+                // k = 0), so the check is made once per unit instead of once per element.
+                // (Power-of-two levels, mode 1, need no check at all: x * 2^-k is exact division.)
+                const bool wholeRow = divMode == 1 || (divMode == 2 && (__float_as_uint(range) == 0u ||
+                                                                             (range > 1e-20f && range < 3.9e17f)));
+                if (st.present && wholeRow) {
+                    auto one = [&](uint32_t k) {
+                        const float x = __fmul_rn(range, static_cast<float>(k));
+                        const float q0 = __fmul_rn(x, p.invLevels);
+                        if (divMode == 1) {
+                            return __fadd_rn(st.mm.x, q0);
+                        }
+                        const float e = __fmaf_rn(-q0, p.levels, x);
+                        return __fadd_rn(st.mm.x, __fmaf_rn(e, p.invLevels, q0));
+                    };
+                    v.x = one(st.packed & 0xff);
+                    v.y = one((st.packed >> 8) & 0xff);
+                    v.z = one((st.packed >> 16) & 0xff);
+                    v.w = one(st.packed >> 24);
+                } else if (st.present) {
+                    v.x = uniformDequant(st.mm.x, range, st.packed & 0xff, p.levels, p.invLevels, divMode);
+                    v.y = uniformDequant(st.mm.x, range, (st.packed >> 8) & 0xff, p.levels, p.invLevels, divMode);
+                    v.z = uniformDequant(st.mm.x, range, (st.packed >> 16) & 0xff, p.levels, p.invLevels, divMode);
+                    v.w = uniformDequant(st.mm.x, range, st.packed >> 24, p.levels, p.invLevels, divMode);
                 }
                 float4* dst = reinterpret_cast<float4*>(st.dst);
                 if (EPI != EPI_WRITE) {
@@ -1240,7 +1265,7 @@ __global__ void uniform_decode_kernel(const UniformParams p, const int32_t* __re
                 }
                 __stcs(dst, v);
             } else {
-                float v = st.present ? uniformDequant(st.mm.x, range, st.packed, p.levels, p.invLevels, p.divMode) : 0.f;
+                float v = st.present ? uniformDequant(st.mm.x, range, st.packed, p.levels, p.invLevels, divMode) : 0.f;
                 if (EPI != EPI_WRITE) {
                     v = applyEpilogue(v, *st.dst, EPI, o.divisor);
                 }

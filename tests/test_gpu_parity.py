@@ -205,6 +205,14 @@ def test_uniform_divisor_modes_extreme_ranges(abi, oracle, workdir, levels):
     maxs[3::11] = -maxs[3::11]                 # max < min: negative range (and -0 products)
     mins[5::13] = np.float32(-0.0)
     maxs[6::17] = np.float32(3.0e38)           # products overflow to inf
+    # ranges on either side of the per-row gate of the 255 path (1e-20, 1e20 / 256) and of the
+    # per-element one (x = range * k around 1e-20 and 1e20)
+    edge = np.array([1e-20, 1.0000001e-20, 9.999999e-21, 3.9e17, 3.8999999e17, 3.9000001e17, 3.90625e17, 3.92e17,
+                     1e20 / 255, 1e20, 4e-23, 1e-22], np.float32)
+    mins[100:100 + len(edge)] = np.float32(0.0)
+    maxs[100:100 + len(edge)] = edge
+    mins[120:120 + len(edge)] = -edge / 2
+    maxs[120:120 + len(edge)] = edge / 2
     path = str(workdir / ("uni_div_%d.bin" % levels))
     membfile_py.write_uniform(path, words, mins, maxs, values, levels)
     reader, want = abi.open_checked(path), oracle.open(path)
