@@ -653,6 +653,22 @@ def extra_configs(args, reader, device, peak):
                            "roofline_frac": rows_u * per_row / (ms_all / 1e3) / 1e9 / peak},
             "algorithmic_bytes_per_row": per_row}
         del uni
+
+    # ---- the `full` storage (K3, src/full_compression.cpp:41-42): 1 M x dim fp32 rows, a pure gather ----
+    rows_f = min(args.rows, 1_000_000)
+    build_table(args, "full", 32, seed=9, rows=rows_f)
+    full = memb_b200.Reader(table_path(args, "full", 32, 9, rows_f), device=device.index)
+    ids_f = torch.from_numpy(np.random.Generator(np.random.PCG64(42)).integers(0, rows_f, n).astype(np.int32)).to(device)
+    ms_ids = _time_launches(lambda: full._impl.decode_ids_into(ids_f.data_ptr(), True, n, buf.data_ptr(), True, stream))
+    ms_all = _time_launches(lambda: full._impl.decode_range_into(0, rows_f, buf.data_ptr(), True, stream))
+    out["full_fp32"] = {
+        "rows": rows_f, "kernel": "full_gather_kernel",
+        "random_ids": {"n": n, "ms": ms_ids, "rows_per_s": n / (ms_ids / 1e3),
+                       "roofline_frac": n * (8 * dim + 4) / (ms_ids / 1e3) / 1e9 / peak},
+        "full_vocab": {"ms": ms_all, "rows_per_s": rows_f / (ms_all / 1e3),
+                       "roofline_frac": rows_f * 8 * dim / (ms_all / 1e3) / 1e9 / peak},
+        "algorithmic_bytes_per_row": 8 * dim}
+    del full, ids_f
     del buf
 
     # ---- configs[4]: ReadersUnion of two trained readers, Zipf lookups ----
