@@ -265,3 +265,57 @@ def test_word_collections_marshal_identically():
         _memb.pack_words((b"abc", np.array([0, 2, 1], np.uint64)))
     with pytest.raises(ValueError):
         _memb.pack_words((b"abc", np.array([0, 4], np.uint64)))
+
+
+def test_converter_cli_matches_the_builder(oracle, workdir):
+    """tools/converter/memb_converter of the reference (flags :39-79, parsing rules :11-33):
+    same flags, header / short lines skipped, bad weights reported, odd-length lines discarded,
+    duplicate words reported -- and the file equals the one built directly with the Builder."""
+    import io
+    import subprocess
+    import sys
+
+    import memb_b200
+    from memb_b200 import converter
+
+    rng = np.random.default_rng(77)
+    words = ["w%d" % i for i in range(60)] + ["é€", "the"]
+    matrix = rng.standard_normal((len(words), 5)).astype(np.float32)
+    text = workdir / "vectors.txt"
+    with open(text, "w") as f:
+        f.write("%d 5\n" % len(words))                      # word2vec header: skipped (two fields)
+        for w, v in zip(words, matrix):
+            f.write(w + " " + " ".join(repr(float(x)) for x in v) + "\n")
+        f.write("odd 1.0 2.0 3.0\n")                         # wrong length: discarded
+        f.write("bad 1.0 x 3.0 4.0 5.0\n")                   # does not parse: reported
+        f.write("w3 " + " ".join(["0.5"] * 5) + "\n")        # duplicate word: reported by the builder
+        f.write("lonely\n")
+    log = io.StringIO()
+    dest = workdir / "converted.bin"
+    written = converter.convert(str(text), str(dest), "trained", 6, out=log)
+    assert written == len(words)
+    messages = log.getvalue()
+    assert "Exception while parsing" in messages and "1 items are discarded" in messages
+    assert "duplicate word w3" in messages
+    direct = memb_b200.Builder(5, "trained", 6)
+    for w, v in zip(words, matrix):
+        direct.add_word(w, np.asarray([repr(float(x)) for x in v], dtype=np.float32))
+    direct_path = workdir / "direct.bin"
+    direct.save(str(direct_path))
+    assert dest.read_bytes() == direct_path.read_bytes()
+    reader = oracle.open(str(dest))
+    assert reader.dim == 5 and reader.keys() == sorted(w.encode("utf-8") for w in words)
+    got = reader.batch_embedding(words)
+    assert np.abs(got - matrix).max() < 0.2  # 64 centroids over N(0,1) values
+    # --max-words counts LINES (header included), like islice in the reference
+    limited = workdir / "limited.bin"
+    assert converter.main(["--from", str(text), "--to", str(limited), "--quantization", "full", "--max-words", "11"]) == 0
+    assert oracle.open(str(limited)).rows == 10
+    script = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "converter", "memb_converter")
+    cli = workdir / "cli.bin"
+    run = subprocess.run([sys.executable, script, "--from", str(text), "--to", str(cli), "--quantization", "uniform",
+                          "--bits-per-weight", "8"], capture_output=True, text=True)
+    assert run.returncode == 0, run.stderr
+    assert "items are discarded" in run.stdout and oracle.open(str(cli)).rows == len(words)
+    with pytest.raises(SystemExit):
+        converter.parse_args(["--from", "a", "--to", "b", "--quantization", "lossless"])
