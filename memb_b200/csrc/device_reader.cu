@@ -29,6 +29,7 @@ std::atomic<uint64_t> g_launches{0};
 std::atomic<int64_t> g_optLutReplicas{0};
 std::atomic<int64_t> g_optWarps{0};
 std::atomic<int64_t> g_optGeneric{0};
+std::atomic<int64_t> g_optPassRows{0};
 
 struct StatusError {
     memb_b200_status status;
@@ -649,6 +650,10 @@ void launchResolve(const memb_b200_reader& r, const char* dQuery, const uint64_t
 // host through the scratch buffer (4 GiB of fp32).
 uint64_t rowsPerPass(uint64_t rowFloats)
 {
+    const uint64_t forced = static_cast<uint64_t>(g_optPassRows.load());  // tests: exercise the multi-pass path
+    if (forced) {
+        return forced;
+    }
     const uint64_t cap = (uint64_t(4) << 30) / (std::max<uint64_t>(rowFloats, 1) * 4);
     return std::max<uint64_t>(cap, 32);
 }
@@ -786,6 +791,8 @@ memb_b200_status memb_b200_set_option(const char* name, int64_t value)
             g_optWarps = value;
         } else if (key == "trained_generic" && (value == 0 || value == 1)) {
             g_optGeneric = value;
+        } else if (key == "host_pass_rows" && value >= 0) {
+            g_optPassRows = value;  // rows staged per pass for host outputs (0 = 4 GiB of fp32)
         } else {
             fail(MEMB_B200_ERR_ARGUMENT, "unknown option or value out of range: " + key);
         }

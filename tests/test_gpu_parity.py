@@ -503,3 +503,25 @@ def test_concurrent_calls_on_one_reader(oracle, synthetic):
     for t in threads:
         t.join()
     assert not failures, failures
+
+
+def test_host_outputs_in_several_passes(abi, oracle, synthetic):
+    """Host outputs larger than the staging buffer (4 GiB of fp32 by default) are decoded in
+    passes; forced down to 100 rows here, for ids, words, ranges and both union modes."""
+    syns = union_case(synthetic)[:2]
+    readers = [abi.open_checked(s.path) for s in syns]
+    oracles = [oracle.open(s.path) for s in syns]
+    rng = np.random.default_rng(3)
+    words = queries_for(syns[0], rng, 777)
+    parts = [o.batch_embedding(words) for o in oracles]
+    ids = rng.integers(-1, readers[0].rows, 1234).astype(np.int32)
+    try:
+        abi.check(abi.lib.memb_b200_set_option(b"host_pass_rows", 100))
+        assert bits_equal(readers[0].lookup_words(words), parts[0])
+        assert bits_equal(readers[0].decode_ids(ids), oracles[0].batch_ids(ids))
+        assert bits_equal(readers[0].decode_range(5, 905), oracles[0].decode_range(5, 905))
+        assert bits_equal(helpers.union_lookup_words(abi, readers, abi.AVERAGE, words, 300), np.mean(parts, axis=0))
+        assert bits_equal(helpers.union_lookup_words(abi, readers, abi.CONCATENATE, words, 600),
+                          np.concatenate(parts, axis=-1))
+    finally:
+        abi.lib.memb_b200_set_option(b"host_pass_rows", 0)
