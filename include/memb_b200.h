@@ -143,9 +143,10 @@ void memb_b200_host_free(void* ptr);
 
 /* Kernels launched by this library in this process so far (bench's gpu_launches). */
 uint64_t memb_b200_launch_count(void);
-/* Tuning knobs for experiments ("trained_lut_replicas" = 0 auto | 1 | 32,
- * "trained_warps" = 0 auto | 1..32, "trained_generic" = 0|1).  Applies to readers
- * opened / calls made afterwards. */
+/* Knobs for experiments and tests: "trained_lut_replicas" = 0 auto | 1 | 32,
+ * "trained_warps" = 0 auto | 1..10, "trained_generic" = 0|1 (one-thread-per-row decode),
+ * "host_pass_rows" = rows staged per pass for host outputs (0 = 4 GiB of fp32).
+ * Applies to readers opened / calls made afterwards. */
 memb_b200_status memb_b200_set_option(const char* name, int64_t value);
 
 /* ---- write side (fixture generator; `_memb.Builder`, python/memb_bindings.cpp:12-34) ---- */
