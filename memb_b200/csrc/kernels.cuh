@@ -376,7 +376,10 @@ constexpr uint32_t TRAINED_TILE_BYTES = 17 * 128;  // 8 groups of 260 B, rounded
 constexpr uint32_t TRAINED_MAX_DIM = 4095;  // consumed bits live in 16 bits: dim * 16 < 65536
 constexpr uint32_t TRAINED_MAX_WARPS = 10;  // measured optimum (sweep r01: 8 -> 2.98, 10 -> 3.22, 12 -> 3.10 G rows/s) ...
 constexpr uint32_t TRAINED_MAX_REGS = 168;  // ... up to three warps on a scheduler, which owns 16384 registers: 3 x 32 x 168 = 16128
-constexpr uint32_t TRAINED_PREFETCH_UNITS = 192 / MEMB_UNIT_BYTES;  // 192 B of the next row per lane held in registers
+#ifndef MEMB_PREFETCH_BYTES
+#define MEMB_PREFETCH_BYTES 192
+#endif
+constexpr uint32_t TRAINED_PREFETCH_UNITS = MEMB_PREFETCH_BYTES / MEMB_UNIT_BYTES;  // bytes of the next row per lane held in registers
 
 __host__ __device__ inline uint32_t trainedLutBytes(uint32_t lutBits, uint32_t replicas)
 {
