@@ -30,6 +30,7 @@ std::atomic<int64_t> g_optLutReplicas{0};
 std::atomic<int64_t> g_optWarps{0};
 std::atomic<int64_t> g_optGeneric{0};
 std::atomic<int64_t> g_optPassRows{0};
+std::atomic<int64_t> g_optSymAverage{1};
 
 struct StatusError {
     memb_b200_status status;
@@ -485,7 +486,7 @@ bool vec4Ok(uint32_t dim, const K::OutputSpec& o)
            reinterpret_cast<uintptr_t>(o.out) % 16 == 0;
 }
 
-template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW, bool SIDE = false>
+template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW, bool SIDE = false, int SYM = 0>
 void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
                          const K::OutputSpec& o, int epi, cudaStream_t stream)
 {
@@ -500,7 +501,7 @@ void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t
     if (tiles + 4ull * grid * r.trainedWarps >= 0xffffffffull) {
         fail(MEMB_B200_ERR_ARGUMENT, "decode: too many rows in one call");
     }
-    auto kernel = K::trained_decode_kernel<G, VEC4, ESCAPE, SMALLCB, RMW, SIDE>;
+    auto kernel = K::trained_decode_kernel<G, VEC4, ESCAPE, SMALLCB, RMW, SIDE, SYM>;
     CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemBytes)));
     uint32_t* counter = r.dTileCounters + (const_cast<memb_b200_reader&>(r).launchSeq++ % memb_b200_reader::TILE_COUNTERS);
     CUDA_CHECK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), stream));
@@ -517,6 +518,17 @@ void launchTrainedVec(const memb_b200_reader& r, const int32_t* ids, uint32_t ro
 {
     const bool small = r.trained.symShift == 2;
     const bool rmw = epi != K::EPI_WRITE;
+    if (o.sym) {
+        // average of trained readers through symbol words (OutputSpec::sym)
+        if (rmw) {
+            small ? launchTrainedKernel<G, true, false, true, true, false, 2>(r, ids, rowBegin, n, o, epi, stream)
+                  : launchTrainedKernel<G, true, false, false, true, false, 2>(r, ids, rowBegin, n, o, epi, stream);
+        } else {
+            small ? launchTrainedKernel<G, true, false, true, false, false, 1>(r, ids, rowBegin, n, o, epi, stream)
+                  : launchTrainedKernel<G, true, false, false, false, false, 1>(r, ids, rowBegin, n, o, epi, stream);
+        }
+        return;
+    }
     if (!rmw && (o.sideHead || o.sideTail)) {
         small ? launchTrainedKernel<G, true, false, true, false, true>(r, ids, rowBegin, n, o, epi, stream)
               : launchTrainedKernel<G, true, false, false, false, true>(r, ids, rowBegin, n, o, epi, stream);
@@ -710,12 +722,34 @@ void launchUnion(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_m
             }
         }
     }
+    // average, first two readers trained: reader 0 leaves symbol words, reader 1 gathers from
+    // them while it writes the row (OutputSpec::sym): one write of the output instead of
+    // write + read + write
+    uint32_t* symWordsBuf = nullptr;
+    auto tiledTrained = [&](const memb_b200_reader& r, const K::OutputSpec& o) {
+        return r.file->storage == STORAGE_TRAINED && r.trainedWarps != 0 && !r.trainedEscape && vec4Ok(r.file->dim, o);
+    };
+    if (mode == MEMB_B200_AVERAGE && n && g_optSymAverage.load() && tiledTrained(*readers[0], specs[0]) &&
+        tiledTrained(*readers[1], specs[1]) && readers[0]->trained.hasZeroSlot) {
+        const uint32_t words = readers[0]->file->dim / 4;
+        CUDA_CHECK(cudaMallocAsync(reinterpret_cast<void**>(&symWordsBuf), n * words * sizeof(uint32_t), stream));
+        for (uint32_t k = 0; k < 2; ++k) {
+            specs[k].sym = symWordsBuf;
+            specs[k].symWords = words;
+        }
+        specs[1].symCodebook = readers[0]->trained.codebook;
+        specs[1].symCodebookSize = readers[0]->trained.codebookSize;
+        specs[1].symFieldShift = 2u - readers[0]->trained.symShift;
+    }
     for (uint32_t k = 0; k < R; ++k) {
         int epi = K::EPI_WRITE;
         if (mode != MEMB_B200_CONCATENATE) {
             epi = k == 0 ? K::EPI_WRITE : (k + 1 == R ? K::EPI_FINALIZE : K::EPI_ACCUMULATE);
         }
         launchDecode(*readers[k], dIds + k * idStride + first, 0, n, specs[k], epi, stream);
+    }
+    if (symWordsBuf) {
+        CUDA_CHECK(cudaFreeAsync(symWordsBuf, stream));
     }
     for (size_t b = 0; b < stitched.size(); ++b) {
         const unsigned grid = static_cast<unsigned>((2 * n + 255) / 256);
@@ -791,6 +825,8 @@ memb_b200_status memb_b200_set_option(const char* name, int64_t value)
             g_optWarps = value;
         } else if (key == "trained_generic" && (value == 0 || value == 1)) {
             g_optGeneric = value;
+        } else if (key == "union_symbol_average" && (value == 0 || value == 1)) {
+            g_optSymAverage = value;
         } else if (key == "host_pass_rows" && value >= 0) {
             g_optPassRows = value;  // rows staged per pass for host outputs (0 = 4 GiB of fp32)
         } else {

@@ -54,6 +54,16 @@ struct OutputSpec {
     // sideTail[i] instead and stitch_sectors_kernel writes the shared sector whole.
     float4* sideHead = nullptr;
     float4* sideTail = nullptr;
+    // average of trained readers: reader 0 does not write fp32 rows at all -- its launch leaves
+    // the SYMBOL words of its rows (dim bytes per row instead of 4 * dim) in `sym`, and the
+    // launch of reader 1 gathers reader 0's centroids from them while it flushes its own
+    // (SYM instantiations of the trained kernel): the output is written once, 1800 instead of
+    // 3600 bytes move per row.  Row i of the launch lives at sym + i * symWords.
+    uint32_t* sym = nullptr;
+    uint32_t symWords = 0;
+    const float* symCodebook = nullptr;  // reader 0's centroids (SYM == 2)
+    uint32_t symCodebookSize = 0;
+    uint32_t symFieldShift = 0;          // reader 0's symbol field -> byte offset into its codebook
 };
 
 // Where the 16 B unit `unit` of output row i goes (see OutputSpec::sideHead).
@@ -357,7 +367,7 @@ struct TrainedParams {
     uint32_t zeroWord;      // ... and this is its symbol field, four times: what a lane WITHOUT a row writes to the tile
 };
 
-constexpr uint32_t TRAINED_CODEBOOK_BYTES = 1024;  // 256 centroids
+constexpr uint32_t TRAINED_CODEBOOK_BYTES = 2048;  // 256 centroids, twice (the second copy: OutputSpec::symCodebook)
 constexpr uint32_t TRAINED_CHUNK = 32;             // symbols decoded between two flushes
 constexpr uint32_t TRAINED_CHUNK_UNITS = TRAINED_CHUNK / 4;       // 16 B output units (= tile words) per chunk and row
 constexpr uint32_t TRAINED_RING_UNITS = 2 * TRAINED_CHUNK_UNITS;  // the tile keeps the last two chunks of every row
@@ -543,6 +553,42 @@ __device__ __forceinline__ float4 gatherCentroids(uint32_t cb, uint32_t s4)
     return v;
 }
 
+// The same for symbol words of ANOTHER reader (field << shift = byte offset into its codebook).
+__device__ __forceinline__ float4 gatherCentroidsShift(uint32_t cb, uint32_t s4, uint32_t shift)
+{
+    float4 v;
+    v.x = ldsF32(cb + ((s4 & 0xffu) << shift));
+    v.y = ldsF32(cb + (((s4 >> 8) & 0xffu) << shift));
+    v.z = ldsF32(cb + (((s4 >> 16) & 0xffu) << shift));
+    v.w = ldsF32(cb + ((s4 >> 24) << shift));
+    return v;
+}
+__device__ __forceinline__ uint32_t ldU32If(bool pred, const uint32_t* ptr)
+{
+    uint32_t v = 0;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.u32 p, %2, 0;\n"
+        "@p ld.global.u32 %0, [%1];\n"
+        "}\n"
+        : "+r"(v)
+        : "l"(ptr), "r"(static_cast<uint32_t>(pred))
+        : "memory");
+    return v;
+}
+__device__ __forceinline__ void stU32If(bool pred, uint32_t* ptr, uint32_t v)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.u32 p, %2, 0;\n"
+        "@p st.global.u32 [%0], %1;\n"
+        "}\n" ::"l"(ptr),
+        "r"(v), "r"(static_cast<uint32_t>(pred))
+        : "memory");
+}
+
 // Decode state of one lane.  lutLane / rowLane are shared-window addresses.
 struct LaneDecoder {
     uint32_t lo, hi;     // window: bit 0 of lo = bit `consumed` of the re-packed row
@@ -601,13 +647,25 @@ __device__ __forceinline__ void decodeWords(LaneDecoder& d, const TrainedParams&
     }
 }
 
+// sum / R of np.mean.  R a power of two (two readers!): sum * 2^-k is the same correctly
+// rounded real number as sum / 2^k, in one instruction instead of the IEEE divide sequence
+// (which tripled the instruction count of the FINALIZE launch: 0.74 -> ms per 1 M rows).
+__device__ __forceinline__ float divideByReaders(float s, float divisor)
+{
+    const uint32_t bits = __float_as_uint(divisor);
+    if ((bits & 0x007fffffu) == 0u) {
+        return __fmul_rn(s, __uint_as_float(0x7f000000u - bits));  // 1 / 2^k
+    }
+    return __fdiv_rn(s, divisor);
+}
+
 __device__ __forceinline__ float applyEpilogue(float v, float old, int epi, float divisor)
 {
     if (epi == EPI_WRITE) {
         return v;
     }
     const float s = __fadd_rn(old, v);
-    return epi == EPI_ACCUMULATE ? s : __fdiv_rn(s, divisor);
+    return epi == EPI_ACCUMULATE ? s : divideByReaders(s, divisor);
 }
 
 // np.mean's add chain on four lanes of a row: old + v, and for the last reader / R.
@@ -618,10 +676,10 @@ __device__ __forceinline__ float4 applyEpilogue4(float4 v, float4 old, int epi, 
     v.z = __fadd_rn(old.z, v.z);
     v.w = __fadd_rn(old.w, v.w);
     if (epi == EPI_FINALIZE) {
-        v.x = __fdiv_rn(v.x, divisor);
-        v.y = __fdiv_rn(v.y, divisor);
-        v.z = __fdiv_rn(v.z, divisor);
-        v.w = __fdiv_rn(v.w, divisor);
+        v.x = divideByReaders(v.x, divisor);
+        v.y = divideByReaders(v.y, divisor);
+        v.z = divideByReaders(v.z, divisor);
+        v.w = divideByReaders(v.w, divisor);
     }
     return v;
 }
@@ -664,7 +722,9 @@ __device__ __forceinline__ uint32_t shflFrom(uint32_t v, uint32_t srcLane)
 // RMW: the launch carries an average epilogue (ACCUMULATE / FINALIZE): the fast flush
 // reads the running sum, adds, divides for the last reader, and stores.
 // SIDE: the launch redirects first / last units to side buffers (OutputSpec::sideHead).
-template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW, bool SIDE>
+// SYM: 1 = the launch stores symbol words instead of fp32 rows, 2 = the running sum it adds to
+// is gathered from another reader's symbol words (OutputSpec::sym).
+template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW, bool SIDE, int SYM>
 __global__ void __maxnreg__(TRAINED_MAX_REGS)
 trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, uint32_t rowBegin, uint64_t n,
                       const OutputSpec o, const int epi, uint32_t* __restrict__ tileCounter)
@@ -717,6 +777,9 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         }
         for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) {
             cbS[i] = i < p.codebookSize ? p.codebook[i] : 0.f;
+            if (SYM == 2) {
+                cbS[256 + i] = i < o.symCodebookSize ? o.symCodebook[i] : 0.f;
+            }
         }
     }
     __syncthreads();
@@ -872,6 +935,10 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         const uint32_t aBase = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(rowPtr0) >> 4);
         const uint32_t aStep = static_cast<uint32_t>(rowBytes >> 4) * TRAINED_FLUSH_ROWS;  // FLUSH_ROWS rows, in 16 B units
         const uint32_t tileRows = tileRowBase(tile, fr);  // rows 4*it + fr: + it * TRAINED_TILE_GROUP_BYTES
+        // SYM: symbol words of row 4*it + fr of this tile start at symRow0 + it * symStep
+        uint32_t* const symRow0 = SYM ? o.sym + (row0 + fr) * o.symWords : nullptr;
+        const uint64_t symStep = static_cast<uint64_t>(TRAINED_FLUSH_ROWS) * o.symWords;
+        const uint32_t cb0 = cb + 1024;  // the other reader's codebook (SYM == 2)
         // A lane without a row (missing word) decodes row 0 like the others but writes the
         // symbol of the codebook's +0.0 slot to the tile, so the straight-line flush needs no
         // per-row predicate: only a ragged last tile (or a codebook with no free slot) takes
@@ -894,7 +961,11 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                 for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
                     const int a = int((aBase + it * aStep) & 7u);
                     const int j = ub - a + int(fq);
-                    prefetchL2If(j >= 0 && j < ua, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j);
+                    if (SYM == 2) {
+                        prefetchL2If(j >= 0 && j < ua, symRow0 + it * symStep + j);
+                    } else {
+                        prefetchL2If(j >= 0 && j < ua, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j);
+                    }
                 }
             }
             if (presentMask) {
@@ -956,7 +1027,11 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int a = int((aBase + it * aStep) & 7u);
                             const int j = unitsBefore - a + int(fq) + shift;
                             const int end = last ? end0 : unitsAfter - a;
-                            old[it] = ldF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j);
+                            if (SYM == 2) {
+                                old[it].x = __uint_as_float(ldU32If(j >= 0 && j < end, symRow0 + it * symStep + j));
+                            } else {
+                                old[it] = ldF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j);
+                            }
                         }
 #pragma unroll
                         for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
@@ -964,7 +1039,9 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int j = unitsBefore - a + int(fq) + shift;
                             const int end = last ? end0 : unitsAfter - a;
                             const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
-                            const float4 v = applyEpilogue4(gatherCentroids<SMALLCB>(cb, s4), old[it], epi, o.divisor);
+                            const float4 sum = SYM == 2 ? gatherCentroidsShift(cb0, __float_as_uint(old[it].x), o.symFieldShift)
+                                                        : old[it];
+                            const float4 v = applyEpilogue4(gatherCentroids<SMALLCB>(cb, s4), sum, epi, o.divisor);
                             stcsF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j, v);
                         }
                     }
@@ -979,6 +1056,10 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int a = int((aBase + it * aStep) & 7u);
                             const int j = unitsBefore - a + int(fq);
                             const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
+                            if (SYM == 1) {
+                                symRow0[it * symStep + j] = s4;
+                                continue;
+                            }
                             const float4 v = gatherCentroids<SMALLCB>(cb, s4);
                             stcsF4(reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j, v);
                         }
@@ -989,6 +1070,10 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int j = unitsBefore - a + int(fq);
                             const int end = last ? unitsAfter : unitsAfter - a;
                             const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
+                            if (SYM == 1) {
+                                stU32If(j >= 0 && j < end, symRow0 + it * symStep + j, s4);
+                                continue;
+                            }
                             const float4 v = gatherCentroids<SMALLCB>(cb, s4);
                             float4* dst = reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j;
                             if (SIDE) {
@@ -1002,6 +1087,10 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                                 const int a = int((aBase + it * aStep) & 7u);
                                 const int j2 = unitsBefore - a + int(fq) + int(TRAINED_CHUNK_UNITS);
                                 const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j2));
+                                if (SYM == 1) {
+                                    stU32If(j2 < unitsAfter, symRow0 + it * symStep + j2, s4);
+                                    continue;
+                                }
                                 const float4 u = gatherCentroids<SMALLCB>(cb, s4);
                                 float4* dst = reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j2;
                                 if (SIDE) {
@@ -1021,6 +1110,11 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int end = last ? unitsAfter : unitsAfter - a;
                             const bool rowPresent = (presentMask >> r) & 1u;
                             for (int j = begin + int(fq); j < end; j += int(TRAINED_CHUNK_UNITS)) {
+                                if (SYM == 1) {
+                                    o.sym[(row0 + r) * o.symWords + j] =
+                                        rowPresent ? ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j)) : p.zeroWord;
+                                    continue;
+                                }
                                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
                                 if (rowPresent) {
                                     v = gatherCentroids<SMALLCB>(
@@ -1031,7 +1125,9 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                                     dst = redirectUnit(o, dst, row0 + r, static_cast<uint32_t>(j), dim / 4 - 1);
                                 }
                                 if (epi != EPI_WRITE) {
-                                    const float4 old = *dst;
+                                    const float4 old = SYM == 2 ? gatherCentroidsShift(cb0, o.sym[(row0 + r) * o.symWords + j],
+                                                                                       o.symFieldShift)
+                                                                : *dst;
                                     v.x = applyEpilogue(v.x, old.x, epi, o.divisor);
                                     v.y = applyEpilogue(v.y, old.y, epi, o.divisor);
                                     v.z = applyEpilogue(v.z, old.z, epi, o.divisor);

@@ -525,3 +525,26 @@ def test_host_outputs_in_several_passes(abi, oracle, synthetic):
                           np.concatenate(parts, axis=-1))
     finally:
         abi.lib.memb_b200_set_option(b"host_pass_rows", 0)
+
+
+@pytest.mark.parametrize("bits0,bits1,dim,n", [(8, 4, 100, 999), (3, 5, 64, 1024), (4, 4, 12, 33), (1, 8, 300, 1500),
+                                               (6, 4, 300, 700)])
+def test_union_average_through_symbol_words(abi, oracle, synthetic, bits0, bits1, dim, n):
+    """average of trained readers: reader 0 leaves symbol words, reader 1 gathers both codebooks
+    (OutputSpec::sym); every codebook size / field format, ragged tiles, missing words on either
+    side, three readers (the third adds to the fp32 sum), and the plain path as a cross-check."""
+    syns = [synthetic("trained", bits0, rows=900, dim=dim, seed=51), synthetic("trained", bits1, rows=800, dim=dim, seed=52),
+            synthetic("trained", 4, rows=700, dim=dim, seed=53)]
+    readers = [abi.open_checked(s.path) for s in syns]
+    oracles = [oracle.open(s.path) for s in syns]
+    rng = np.random.default_rng(n)
+    words = sum([queries_for(s, rng, n // 3 + 1) for s in syns], [])[:n]
+    parts = [o.batch_embedding(words) for o in oracles]
+    for count in (2, 3):
+        want = np.mean(parts[:count], axis=0)
+        assert bits_equal(helpers.union_lookup_words(abi, readers[:count], abi.AVERAGE, words, dim), want)
+        try:
+            abi.check(abi.lib.memb_b200_set_option(b"union_symbol_average", 0))
+            assert bits_equal(helpers.union_lookup_words(abi, readers[:count], abi.AVERAGE, words, dim), want)
+        finally:
+            abi.lib.memb_b200_set_option(b"union_symbol_average", 1)
