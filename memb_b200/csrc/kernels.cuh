@@ -650,11 +650,27 @@ __device__ __forceinline__ void decodeWords(LaneDecoder& d, const TrainedParams&
 // sum / R of np.mean.  R a power of two (two readers!): sum * 2^-k is the same correctly
 // rounded real number as sum / 2^k, in one instruction instead of the IEEE divide sequence
 // (which tripled the instruction count of the FINALIZE launch: 0.74 -> ms per 1 M rows).
+// R = 3, 5, 6, 7: the constant-divisor sequence of divideByLevels (q0 = s * RN(1/R), one FMA
+// residual, one FMA correction), verified EXHAUSTIVELY on the host against s / R for every
+// float with 1e-20 < |s| < 1e20 and for +0 (scripts/divconst_exhaustive.c: 0 mismatches of
+// 2.23e9 per divisor; -0 is NOT in the set: the sequence returns +0 for it).  Sums outside
+// that set, and every other R, take the IEEE divide.  RN(1/R) is formed once per thread
+// (it depends on the launch parameter only).
 __device__ __forceinline__ float divideByReaders(float s, float divisor)
 {
     const uint32_t bits = __float_as_uint(divisor);
     if ((bits & 0x007fffffu) == 0u) {
         return __fmul_rn(s, __uint_as_float(0x7f000000u - bits));  // 1 / 2^k
+    }
+    if (divisor <= 7.0f) {  // 3, 5, 6, 7 (R is an integer >= 2 and not a power of two here)
+        const float inv = __frcp_rn(divisor);
+        const float q0 = __fmul_rn(s, inv);
+        const float e = __fmaf_rn(-q0, divisor, s);
+        const float q1 = __fmaf_rn(e, inv, q0);
+        const float as = fabsf(s);
+        if ((as > 1e-20f && as < 1e20f) || __float_as_uint(s) == 0u) {
+            return q1;
+        }
     }
     return __fdiv_rn(s, divisor);
 }

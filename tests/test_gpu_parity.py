@@ -275,6 +275,22 @@ def union_case(synthetic):
     return [a, b, c, d]
 
 
+@pytest.mark.parametrize("count", [5, 6, 7, 9])
+def test_union_average_small_divisors(abi, oracle, synthetic, count):
+    """np.mean over R = 5, 6, 7 readers takes the constant-divisor sequence of divideByReaders
+    (verified exhaustively on the host, scripts/divconst_exhaustive.c), R = 9 the IEEE divide;
+    sums that are exactly zero (words missing everywhere) and mixed storages included."""
+    kinds = [("trained", 4), ("trained", 5), ("uniform", 8), ("full", 8), ("trained", 3), ("uniform", 4), ("trained", 6),
+             ("full", 8), ("trained", 2)]
+    syns = [synthetic(k, b, rows=600 + 50 * i, dim=60, seed=70 + i) for i, (k, b) in enumerate(kinds[:count])]
+    readers = [abi.open_checked(s.path) for s in syns]
+    oracles = [oracle.open(s.path) for s in syns]
+    rng = np.random.default_rng(count)
+    words = sum([queries_for(s, rng, 150) for s in syns], [])
+    want = np.mean([o.batch_embedding(words) for o in oracles], axis=0)
+    assert bits_equal(helpers.union_lookup_words(abi, readers, abi.AVERAGE, words, 60), want)
+
+
 @pytest.mark.parametrize("count", [2, 3, 4])
 def test_union_average_and_concatenate(abi, oracle, synthetic, count):
     syns = union_case(synthetic)[:count]
