@@ -31,6 +31,7 @@ std::atomic<int64_t> g_optWarps{0};
 std::atomic<int64_t> g_optGeneric{0};
 std::atomic<int64_t> g_optPassRows{0};
 std::atomic<int64_t> g_optSymAverage{1};
+std::atomic<int64_t> g_optUniformRows{1};  // dense uniform lookups: uniform_rows_kernel (0 = element walk)
 
 struct StatusError {
     memb_b200_status status;
@@ -415,7 +416,6 @@ void loadTrained(memb_b200_reader& r)
         warps = 0;
     }
     r.trainedWarps = warps;
-    CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&r.dTileCounters), memb_b200_reader::TILE_COUNTERS * sizeof(uint32_t)));
 
     r.stats.max_code_len = maxLen;
     r.stats.lut_bits = lutBits;
@@ -611,6 +611,25 @@ void launchDecode(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBeg
         auto go = [&](auto kernel) { kernel<<<flatGrid, 256, 0, stream>>>(r.uniform, ids, rowBegin, n, o); };
         if (vec && epi == K::EPI_WRITE && (o.sideHead || o.sideTail)) {
             go(K::uniform_decode_kernel<true, K::EPI_WRITE, true>);
+        } else if (vec && epi == K::EPI_WRITE && o.rowStride == dim && o.colOffset == 0 && dim >= 8 && dim <= 8188 &&
+                   g_optUniformRows.load() != 0) {
+            // dense result: per-row work once per row, a group ahead (uniform_rows_kernel)
+            auto rows = [&](auto kernel) {
+                static int perSM = 0;  // same for every device of this process (one architecture)
+                if (perSM == 0) {
+                    int b = 0;
+                    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, kernel, K::UNIFORM_ROWS_WARPS * 32, 0);
+                    perSM = b > 0 ? b : 4;
+                }
+                constexpr unsigned W = K::UNIFORM_ROWS_WARPS;  // one 32-row group per warp at a time
+                const unsigned grid = static_cast<unsigned>(std::min<uint64_t>(((n + 31) / 32 + W - 1) / W, uint64_t(r.numSMs) * perSM));
+                uint32_t* counter = r.dTileCounters + (const_cast<memb_b200_reader&>(r).launchSeq++ % memb_b200_reader::TILE_COUNTERS);
+                CUDA_CHECK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), stream));
+                kernel<<<grid, W * 32, 0, stream>>>(r.uniform, ids, rowBegin, n, o.out, counter);
+            };
+            r.uniform.divMode == 1   ? rows(K::uniform_rows_kernel<1>)
+            : r.uniform.divMode == 2 ? rows(K::uniform_rows_kernel<2>)
+                                     : rows(K::uniform_rows_kernel<0>);
         } else if (vec && epi == K::EPI_WRITE) {
             r.uniform.divMode == 1   ? go(K::uniform_decode_kernel<true, K::EPI_WRITE, false, 1>)
             : r.uniform.divMode == 2 ? go(K::uniform_decode_kernel<true, K::EPI_WRITE, false, 2>)
@@ -827,6 +846,8 @@ memb_b200_status memb_b200_set_option(const char* name, int64_t value)
             g_optGeneric = value;
         } else if (key == "union_symbol_average" && (value == 0 || value == 1)) {
             g_optSymAverage = value;
+        } else if (key == "uniform_rows_kernel" && (value == 0 || value == 1)) {
+            g_optUniformRows = value;
         } else if (key == "host_pass_rows" && value >= 0) {
             g_optPassRows = value;  // rows staged per pass for host outputs (0 = 4 GiB of fp32)
         } else {
@@ -895,6 +916,9 @@ memb_b200_status memb_b200_open(const char* path, int device, unsigned num_threa
             cudaGetLastError();
         }
 
+        // work counters of the dynamically scheduled kernels (trained tiles, uniform row groups)
+        CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&reader->dTileCounters),
+                              memb_b200_reader::TILE_COUNTERS * sizeof(uint32_t)));
         const auto t1 = std::chrono::steady_clock::now();
         buildVocabulary(*reader);
         reader->stats.upload_ms += msSince(t1);

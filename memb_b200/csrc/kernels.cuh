@@ -1409,6 +1409,153 @@ __global__ void uniform_decode_kernel(const UniformParams p, const int32_t* __re
         });
 }
 
+// K2, plain lookup into a dense (n x dim) result (rowStride == dim, no column offset, dim a
+// multiple of 4 up to 8188): the form Reader.batch_embedding / decode_range launch.
+// ncu r01 of the element-walk kernel above: 95 thread instructions per 16 B unit, 69 % of the
+// issue slots, and with random ids every one of a row's 75 units walked the dependent chain
+// id -> (min, max) -> payload.  Here a WARP owns a group of 32 consecutive output rows and the
+// per-row work is done once per row, by the lane of that number, a group AHEAD of the units
+// that need it: id (two groups ahead), then (min, max), range and the division gate (one group
+// ahead) go to the warp's double-buffered shared table {payload word offset, min, range, mode}.
+// A unit then is multiply-high -> LDS.128 -> one payload load -> dequant -> one 128-bit
+// streaming store at a LINEAR address (512 contiguous bytes per warp store).  No block barrier:
+// warps run their own pipelines (a first version with a 256-thread group and __syncthreads
+// lost 7 % at 4 bits to the barrier).
+// Same arithmetic, same order as uniform_decode_kernel (bit-identical results).
+constexpr int UNIFORM_ROWS_BATCH = 5;     // units in flight per lane: 15 passes of 5 x 32 cover 32 rows x 75 units
+constexpr int UNIFORM_ROWS_WARPS = 8;
+
+template <int DIV>
+__global__ void __launch_bounds__(UNIFORM_ROWS_WARPS * 32)
+uniform_rows_kernel(const UniformParams p, const int32_t* __restrict__ ids, uint32_t rowBegin, uint64_t n,
+                    float* __restrict__ out, uint32_t* __restrict__ groupCounter)
+{
+    // x: first payload word of the row, y: min, z: range, w: 0 missing / 1 gated fast form / 2 per-element form
+    __shared__ uint4 infoAll[UNIFORM_ROWS_WARPS][2][32];
+    const uint32_t perRow = p.dim / 4;
+    const uint32_t inv = 0xffffffffu / perRow + 1;  // floor(t / perRow) == umulhi(t, inv) for t < 2^21
+    const uint32_t lane = threadIdx.x & 31u;
+    uint4(*info)[32] = infoAll[threadIdx.x >> 5];
+    const uint64_t groups = (n + 31) / 32;
+    const uint64_t step = static_cast<uint64_t>(gridDim.x) * UNIFORM_ROWS_WARPS;
+    const uint32_t* __restrict__ payload = reinterpret_cast<const uint32_t*>(p.values);
+
+    auto loadId = [&](uint64_t g) -> int64_t {
+        const uint64_t i = g * 32 + lane;
+        if (g >= groups || i >= n) {
+            return -1;
+        }
+        return ids ? static_cast<int64_t>(__ldg(ids + i)) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
+    };
+    auto loadMinMax = [&](int64_t row) {
+        return row >= 0 && row < static_cast<int64_t>(p.rows) ? __ldg(p.minmax + row) : make_float2(0.f, 0.f);
+    };
+    auto makeInfo = [&](int64_t row, float2 mm) {
+        uint4 r;
+        const bool present = row >= 0 && row < static_cast<int64_t>(p.rows);
+        const float range = __fsub_rn(mm.y, mm.x);
+        // the gate of uniform_decode_kernel, once per row
+        const bool wholeRow = DIV == 1 || (DIV == 2 && (__float_as_uint(range) == 0u || (range > 1e-20f && range < 3.9e17f)));
+        r.x = present ? static_cast<uint32_t>(row) * perRow : 0u;
+        r.y = __float_as_uint(mm.x);
+        r.z = __float_as_uint(range);
+        r.w = !present ? 0u : wholeRow ? 1u : 2u;
+        return r;
+    };
+
+    // group queue of this warp: g (units being written), gNext (ids loaded, min/max loading),
+    // gAfter (ids loading); the first three are static, later ones come from a ticket counter
+    // (groupCounter, zeroed before the launch) drawn one group before it is needed, exactly as
+    // the trained kernel draws its tiles -- with a static stride the last of the ~7 (random
+    // 1 M) or ~13 (2 M rows) groups per warp ran on a half-empty GPU.
+    uint64_t g = static_cast<uint64_t>(blockIdx.x) * UNIFORM_ROWS_WARPS + (threadIdx.x >> 5);
+    if (g >= groups) {
+        return;
+    }
+    uint64_t gNext = g + step, gAfter = gNext + step;
+    uint32_t ticket = 0, ticketLane = 0;
+    auto drawTicket = [&]() {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "elect.sync %1|p, 0xffffffff;\n"
+            "@p atom.global.add.u32 %0, [%2], 1;\n"
+            "}\n"
+            : "+r"(ticket), "=r"(ticketLane)
+            : "l"(groupCounter)
+            : "memory");
+    };
+    drawTicket();
+    const int64_t row0 = loadId(g);
+    info[0][lane] = makeInfo(row0, loadMinMax(row0));
+    int64_t rowNext = loadId(gNext);
+    __syncwarp();
+    uint32_t buf = 0;
+    for (; g < groups; buf ^= 1u) {
+        const uint64_t gAfter2 = 3 * step + shflFrom(ticket, ticketLane);
+        drawTicket();
+        const float2 mmNext = loadMinMax(rowNext);  // consumed after the units of this group
+        const int64_t rowAfter = loadId(gAfter);
+        const uint64_t rowBase = g * 32;
+        const uint32_t rowsHere = static_cast<uint32_t>(min(static_cast<uint64_t>(32), n - rowBase));
+        const uint32_t elems = rowsHere * perRow;
+        float4* __restrict__ dst = reinterpret_cast<float4*>(out) + rowBase * perRow;
+        for (uint32_t t0 = lane; t0 < elems; t0 += UNIFORM_ROWS_BATCH * 32) {
+            uint4 inf[UNIFORM_ROWS_BATCH];
+            uint32_t packed[UNIFORM_ROWS_BATCH];
+#pragma unroll
+            for (int k = 0; k < UNIFORM_ROWS_BATCH; ++k) {
+                const uint32_t t = t0 + k * 32;
+                packed[k] = 0;
+                if (t < elems) {
+                    const uint32_t r = __umulhi(t, inv);
+                    inf[k] = info[buf][r];
+                    if (inf[k].w) {
+                        packed[k] = __ldg(payload + inf[k].x + (t - r * perRow));
+                    }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < UNIFORM_ROWS_BATCH; ++k) {
+                const uint32_t t = t0 + k * 32;
+                if (t < elems) {
+                    const float mn = __uint_as_float(inf[k].y), range = __uint_as_float(inf[k].z);
+                    const uint32_t q = packed[k];
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (inf[k].w == 1u) {
+                        auto one = [&](uint32_t kk) {
+                            const float x = __fmul_rn(range, static_cast<float>(kk));
+                            const float q0 = __fmul_rn(x, p.invLevels);
+                            if (DIV == 1) {
+                                return __fadd_rn(mn, q0);
+                            }
+                            const float e = __fmaf_rn(-q0, p.levels, x);
+                            return __fadd_rn(mn, __fmaf_rn(e, p.invLevels, q0));
+                        };
+                        v.x = one(q & 0xff);
+                        v.y = one((q >> 8) & 0xff);
+                        v.z = one((q >> 16) & 0xff);
+                        v.w = one(q >> 24);
+                    } else if (inf[k].w == 2u) {
+                        v.x = uniformDequant(mn, range, q & 0xff, p.levels, p.invLevels, DIV);
+                        v.y = uniformDequant(mn, range, (q >> 8) & 0xff, p.levels, p.invLevels, DIV);
+                        v.z = uniformDequant(mn, range, (q >> 16) & 0xff, p.levels, p.invLevels, DIV);
+                        v.w = uniformDequant(mn, range, q >> 24, p.levels, p.invLevels, DIV);
+                    }
+                    __stcs(dst + t, v);
+                }
+            }
+        }
+        // info[buf ^ 1] was last read a group ago, before the previous __syncwarp
+        info[buf ^ 1u][lane] = makeInfo(rowNext, mmNext);
+        rowNext = rowAfter;
+        g = gNext;
+        gNext = gAfter;
+        gAfter = gAfter2;
+        __syncwarp();
+    }
+}
+
 // --------------------------------------------------------------- K3 full ----
 struct FullParams {
     const float* values;  // rows x dim

@@ -17,11 +17,14 @@ def main():
     p.add_argument("--storage", default="uniform")
     p.add_argument("--rows", type=int, default=2_000_000)
     p.add_argument("--reps", type=int, default=20)
+    p.add_argument("--rows-kernel", type=int, default=1, help="0: element walk, 1: uniform_rows_kernel")
     a = p.parse_args()
     import torch
 
     import memb_b200
 
+    from memb_b200 import _memb
+    _memb.set_option("uniform_rows_kernel", a.rows_kernel)
     sys.argv = [sys.argv[0]]
     args = bench.parse_args()
     device = torch.device("cuda", 0)

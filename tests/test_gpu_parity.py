@@ -171,6 +171,32 @@ def test_uniform_parity(abi, oracle, synthetic, bits):
     assert bits_equal(reader.lookup_words(words), want.batch_embedding(words))
 
 
+@pytest.mark.parametrize("bits,dim", [(8, 8), (8, 12), (4, 300), (8, 300), (2, 1024), (8, 8188)])
+def test_uniform_rows_kernel_against_element_walk(abi, oracle, synthetic, bits, dim):
+    """Dense uniform lookups run through uniform_rows_kernel (per-row table in shared memory,
+    filled a 32-row group ahead); option uniform_rows_kernel = 0 sends the same call through the
+    element walk.  Both must equal the oracle bit for bit: ragged batches, one to many groups
+    per block, missing and out-of-range ids, sub-ranges."""
+    rows = 700 if dim <= 1024 else 70
+    syn = synthetic("uniform", bits, rows=rows, dim=dim, seed=60 + bits)
+    reader, want = abi.open_checked(syn.path), oracle.open(syn.path)
+    rng = np.random.default_rng(dim)
+    table = want.decode_range(0, rows)
+    for option in (1, 0):
+        try:
+            abi.check(abi.lib.memb_b200_set_option(b"uniform_rows_kernel", option))
+            assert bits_equal(reader.decode_range(0, rows), table)
+            assert bits_equal(reader.decode_range(rows // 3, rows // 3 + 45), table[rows // 3:rows // 3 + 45])
+            for n in (1, 31, 32, 33, 1000, 40000 if dim <= 300 else 100):
+                ids = rng.integers(0, rows, n).astype(np.int32)
+                ids[::7] = -1
+                ids[3::11] = rows + 5
+                expect = np.where(((ids >= 0) & (ids < rows))[:, None], table[np.clip(ids, 0, rows - 1)], np.float32(0))
+                assert bits_equal(reader.decode_ids(ids), expect)
+        finally:
+            abi.lib.memb_b200_set_option(b"uniform_rows_kernel", 1)
+
+
 def test_uniform_omitted_fields_and_odd_dim(abi, oracle, workdir):
     rng = np.random.default_rng(4)
     rows, dim = 500, 37
