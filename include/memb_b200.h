@@ -146,7 +146,7 @@ uint64_t memb_b200_launch_count(void);
 /* Knobs for experiments and tests: "trained_lut_replicas" = 0 auto | 1 | 32,
  * "trained_warps" = 0 auto | 1..10, "trained_generic" = 0|1 (one-thread-per-row decode),
  * "union_symbol_average" = 0|1 (average of trained readers through symbol words),
- * "uniform_rows_kernel" = 0|1 (dense uniform lookups through the per-row-table kernel; 0 = element walk),
+ * "uniform_rows_kernel" = 0 element walk | 1 auto (row-group kernel unless levels is a power of two) | 2 always,
  * "host_pass_rows" = rows staged per pass for host outputs (0 = 4 GiB of fp32).
  * Applies to readers opened / calls made afterwards. */
 memb_b200_status memb_b200_set_option(const char* name, int64_t value);

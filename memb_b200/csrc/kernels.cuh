@@ -1276,14 +1276,38 @@ __device__ __forceinline__ void forEachElement(uint64_t n, uint32_t perRow, Load
 
 constexpr int FLAT_BATCH = 4;  // elements in flight per thread in K2/K3
 
+// Load time: (values rows x dim, minmax rows) -> records (UniformParams).  One thread per byte.
+__global__ void interleave_uniform_kernel(const uint8_t* __restrict__ values, const float2* __restrict__ minmax,
+                                          uint32_t rows, uint32_t dim, uint32_t stride, uint8_t* __restrict__ records)
+{
+    const uint64_t total = static_cast<uint64_t>(rows) * stride;
+    for (uint64_t b = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; b < total;
+         b += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+        const uint64_t row = b / stride;
+        const uint32_t off = static_cast<uint32_t>(b - row * stride);
+        uint8_t v = 0;
+        if (off < 8) {
+            v = reinterpret_cast<const uint8_t*>(minmax + row)[off];
+        } else if (off - 8 < dim) {
+            v = values[row * dim + (off - 8)];
+        }
+        records[b] = v;
+    }
+}
+
 // ------------------------------------------------------------ K2 uniform ----
 // values: rows x dim bytes (dense, flattened at load from the per-word tables),
 // minmax: rows x (min, max).  out[i] = min + (max - min) * float(v) / levels,
 // evaluated sub -> mul -> div -> add in binary32 round-to-nearest exactly like
 // src/uniform_compression.cpp:68-72 (no FMA contraction, no fast division).
 struct UniformParams {
-    const uint8_t* values;
-    const float2* minmax;
+    // one RECORD per row: {float min, float max, dim quantised bytes, zero padding}, `stride` bytes
+    // apart (a multiple of 64 for records of 256 B and more, of 16 below).  Interleaved at load:
+    // with (min, max) in an array of its own a random row cost a DRAM access of its own, and a
+    // 300 B payload row at an odd offset touched 11 sectors (ncu r01, 1 M random ids of the SoA
+    // layout: 474 B read per row for 312 B of use).  dim 300: 320 B records, 5 whole 64 B pairs.
+    const uint8_t* records;
+    uint32_t stride;
     uint32_t rows;
     uint32_t dim;
     float levels;
@@ -1352,9 +1376,9 @@ __global__ void uniform_decode_kernel(const UniformParams p, const int32_t* __re
             st.mm = make_float2(0.f, 0.f);
             st.packed = 0;
             if (st.present) {
-                const uint8_t* src = p.values + static_cast<uint64_t>(row) * p.dim;
-                st.packed = VEC4 ? __ldg(reinterpret_cast<const uint32_t*>(src) + c) : static_cast<uint32_t>(__ldg(src + c));
-                st.mm = __ldg(p.minmax + row);
+                const uint8_t* rec = p.records + static_cast<uint64_t>(row) * p.stride;
+                st.packed = VEC4 ? __ldg(reinterpret_cast<const uint32_t*>(rec + 8) + c) : static_cast<uint32_t>(__ldg(rec + 8 + c));
+                st.mm = __ldg(reinterpret_cast<const float2*>(rec));
             }
             return st;
         },
@@ -1412,33 +1436,45 @@ __global__ void uniform_decode_kernel(const UniformParams p, const int32_t* __re
 // K2, plain lookup into a dense (n x dim) result (rowStride == dim, no column offset, dim a
 // multiple of 4 up to 8188): the form Reader.batch_embedding / decode_range launch.
 // ncu r01 of the element-walk kernel above: 95 thread instructions per 16 B unit, 69 % of the
-// issue slots, and with random ids every one of a row's 75 units walked the dependent chain
-// id -> (min, max) -> payload.  Here a WARP owns a group of 32 consecutive output rows and the
-// per-row work is done once per row, by the lane of that number, a group AHEAD of the units
-// that need it: id (two groups ahead), then (min, max), range and the division gate (one group
-// ahead) go to the warp's double-buffered shared table {payload word offset, min, range, mode}.
-// A unit then is multiply-high -> LDS.128 -> one payload load -> dequant -> one 128-bit
-// streaming store at a LINEAR address (512 contiguous bytes per warp store).  No block barrier:
-// warps run their own pipelines (a first version with a 256-thread group and __syncthreads
-// lost 7 % at 4 bits to the barrier).
+// issue slots at 8 bits, and with random ids every one of a row's 75 units walked the dependent
+// chain id -> record.  Here a WARP owns a group of 32 consecutive output rows; the lane of a
+// row's number turns its id into the record's word offset a group AHEAD (ids are loaded two
+// groups ahead) and leaves it in the warp's double-buffered shared table.  A unit then is
+// multiply-high -> LDS -> (min, max) + payload word of the SAME record, issued together ->
+// dequant -> one 128-bit streaming store at a LINEAR address (512 contiguous bytes per warp
+// store).  No block barrier: warps run their own pipelines, groups are drawn from a ticket
+// counter.  Measured on the way (B200, 1 M random ids / 2 M-row full vocabulary, 8 bit):
+//   element walk, separate (min, max) array   0.351 / 0.575 ms
+//   256-thread groups, __syncthreads          0.338 / 0.561 ms
+//   warp groups, static stride                0.296 / 0.532 ms
+//   + ticket counter                          0.297 / 0.509 ms
+//   + records, (min, max) read a group ahead  0.300 / 0.562 ms  (the early 8 B read opens the
+//     record's DRAM page a second time; reading it WITH the payload is what the records are for)
 // Same arithmetic, same order as uniform_decode_kernel (bit-identical results).
-constexpr int UNIFORM_ROWS_BATCH = 5;     // units in flight per lane: 15 passes of 5 x 32 cover 32 rows x 75 units
+#ifndef MEMB_UNIFORM_ROWS_BATCH
+#define MEMB_UNIFORM_ROWS_BATCH 5
+#endif
+constexpr int UNIFORM_ROWS_BATCH = MEMB_UNIFORM_ROWS_BATCH;  // units in flight per lane: 15 passes of 5 x 32 cover 32 rows x 75 units
 constexpr int UNIFORM_ROWS_WARPS = 8;
+#ifndef MEMB_UNIFORM_ROWS_MINBLOCKS
+#define MEMB_UNIFORM_ROWS_MINBLOCKS 4
+#endif
 
 template <int DIV>
-__global__ void __launch_bounds__(UNIFORM_ROWS_WARPS * 32)
+__global__ void __launch_bounds__(UNIFORM_ROWS_WARPS * 32, MEMB_UNIFORM_ROWS_MINBLOCKS)
 uniform_rows_kernel(const UniformParams p, const int32_t* __restrict__ ids, uint32_t rowBegin, uint64_t n,
                     float* __restrict__ out, uint32_t* __restrict__ groupCounter)
 {
-    // x: first payload word of the row, y: min, z: range, w: 0 missing / 1 gated fast form / 2 per-element form
-    __shared__ uint4 infoAll[UNIFORM_ROWS_WARPS][2][32];
+    // first word of the row's record; 0xffffffff: no such row (zeros)
+    __shared__ uint32_t infoAll[UNIFORM_ROWS_WARPS][2][32];
     const uint32_t perRow = p.dim / 4;
     const uint32_t inv = 0xffffffffu / perRow + 1;  // floor(t / perRow) == umulhi(t, inv) for t < 2^21
     const uint32_t lane = threadIdx.x & 31u;
-    uint4(*info)[32] = infoAll[threadIdx.x >> 5];
+    uint32_t(*info)[32] = infoAll[threadIdx.x >> 5];
     const uint64_t groups = (n + 31) / 32;
     const uint64_t step = static_cast<uint64_t>(gridDim.x) * UNIFORM_ROWS_WARPS;
-    const uint32_t* __restrict__ payload = reinterpret_cast<const uint32_t*>(p.values);
+    const uint32_t* __restrict__ words = reinterpret_cast<const uint32_t*>(p.records);
+    const uint32_t strideWords = p.stride / 4;
 
     auto loadId = [&](uint64_t g) -> int64_t {
         const uint64_t i = g * 32 + lane;
@@ -1447,24 +1483,12 @@ uniform_rows_kernel(const UniformParams p, const int32_t* __restrict__ ids, uint
         }
         return ids ? static_cast<int64_t>(__ldg(ids + i)) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
     };
-    auto loadMinMax = [&](int64_t row) {
-        return row >= 0 && row < static_cast<int64_t>(p.rows) ? __ldg(p.minmax + row) : make_float2(0.f, 0.f);
-    };
-    auto makeInfo = [&](int64_t row, float2 mm) {
-        uint4 r;
-        const bool present = row >= 0 && row < static_cast<int64_t>(p.rows);
-        const float range = __fsub_rn(mm.y, mm.x);
-        // the gate of uniform_decode_kernel, once per row
-        const bool wholeRow = DIV == 1 || (DIV == 2 && (__float_as_uint(range) == 0u || (range > 1e-20f && range < 3.9e17f)));
-        r.x = present ? static_cast<uint32_t>(row) * perRow : 0u;
-        r.y = __float_as_uint(mm.x);
-        r.z = __float_as_uint(range);
-        r.w = !present ? 0u : wholeRow ? 1u : 2u;
-        return r;
+    auto recordWord = [&](int64_t row) {  // records hold < 2^32 words (loader checks)
+        return row >= 0 && row < static_cast<int64_t>(p.rows) ? static_cast<uint32_t>(row) * strideWords : 0xffffffffu;
     };
 
-    // group queue of this warp: g (units being written), gNext (ids loaded, min/max loading),
-    // gAfter (ids loading); the first three are static, later ones come from a ticket counter
+    // group queue of this warp: g (units being written), gNext (ids loaded), gAfter (ids
+    // loading); the first three are static, later ones come from a ticket counter
     // (groupCounter, zeroed before the launch) drawn one group before it is needed, exactly as
     // the trained kernel draws its tiles -- with a static stride the last of the ~7 (random
     // 1 M) or ~13 (2 M rows) groups per warp ran on a half-empty GPU.
@@ -1486,32 +1510,35 @@ uniform_rows_kernel(const UniformParams p, const int32_t* __restrict__ ids, uint
             : "memory");
     };
     drawTicket();
-    const int64_t row0 = loadId(g);
-    info[0][lane] = makeInfo(row0, loadMinMax(row0));
+    info[0][lane] = recordWord(loadId(g));
     int64_t rowNext = loadId(gNext);
     __syncwarp();
     uint32_t buf = 0;
     for (; g < groups; buf ^= 1u) {
         const uint64_t gAfter2 = 3 * step + shflFrom(ticket, ticketLane);
         drawTicket();
-        const float2 mmNext = loadMinMax(rowNext);  // consumed after the units of this group
-        const int64_t rowAfter = loadId(gAfter);
+        const int64_t rowAfter = loadId(gAfter);  // consumed a group later
         const uint64_t rowBase = g * 32;
         const uint32_t rowsHere = static_cast<uint32_t>(min(static_cast<uint64_t>(32), n - rowBase));
         const uint32_t elems = rowsHere * perRow;
         float4* __restrict__ dst = reinterpret_cast<float4*>(out) + rowBase * perRow;
         for (uint32_t t0 = lane; t0 < elems; t0 += UNIFORM_ROWS_BATCH * 32) {
-            uint4 inf[UNIFORM_ROWS_BATCH];
+            float2 mm[UNIFORM_ROWS_BATCH];
             uint32_t packed[UNIFORM_ROWS_BATCH];
+            bool present[UNIFORM_ROWS_BATCH];
 #pragma unroll
             for (int k = 0; k < UNIFORM_ROWS_BATCH; ++k) {
                 const uint32_t t = t0 + k * 32;
                 packed[k] = 0;
+                mm[k] = make_float2(0.f, 0.f);
+                present[k] = false;
                 if (t < elems) {
                     const uint32_t r = __umulhi(t, inv);
-                    inf[k] = info[buf][r];
-                    if (inf[k].w) {
-                        packed[k] = __ldg(payload + inf[k].x + (t - r * perRow));
+                    const uint32_t w = info[buf][r];
+                    present[k] = w != 0xffffffffu;
+                    if (present[k]) {
+                        mm[k] = __ldg(reinterpret_cast<const float2*>(words + w));
+                        packed[k] = __ldg(words + w + 2 + (t - r * perRow));
                     }
                 }
             }
@@ -1519,10 +1546,12 @@ uniform_rows_kernel(const UniformParams p, const int32_t* __restrict__ ids, uint
             for (int k = 0; k < UNIFORM_ROWS_BATCH; ++k) {
                 const uint32_t t = t0 + k * 32;
                 if (t < elems) {
-                    const float mn = __uint_as_float(inf[k].y), range = __uint_as_float(inf[k].z);
+                    const float mn = mm[k].x, range = __fsub_rn(mm[k].y, mm[k].x);
                     const uint32_t q = packed[k];
+                    // the gate of uniform_decode_kernel
+                    const bool wholeRow = DIV == 1 || (DIV == 2 && (__float_as_uint(range) == 0u || (range > 1e-20f && range < 3.9e17f)));
                     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (inf[k].w == 1u) {
+                    if (present[k] && wholeRow) {
                         auto one = [&](uint32_t kk) {
                             const float x = __fmul_rn(range, static_cast<float>(kk));
                             const float q0 = __fmul_rn(x, p.invLevels);
@@ -1536,7 +1565,7 @@ uniform_rows_kernel(const UniformParams p, const int32_t* __restrict__ ids, uint
                         v.y = one((q >> 8) & 0xff);
                         v.z = one((q >> 16) & 0xff);
                         v.w = one(q >> 24);
-                    } else if (inf[k].w == 2u) {
+                    } else if (present[k]) {
                         v.x = uniformDequant(mn, range, q & 0xff, p.levels, p.invLevels, DIV);
                         v.y = uniformDequant(mn, range, (q >> 8) & 0xff, p.levels, p.invLevels, DIV);
                         v.z = uniformDequant(mn, range, (q >> 16) & 0xff, p.levels, p.invLevels, DIV);
@@ -1547,7 +1576,7 @@ uniform_rows_kernel(const UniformParams p, const int32_t* __restrict__ ids, uint
             }
         }
         // info[buf ^ 1] was last read a group ago, before the previous __syncwarp
-        info[buf ^ 1u][lane] = makeInfo(rowNext, mmNext);
+        info[buf ^ 1u][lane] = recordWord(rowNext);
         rowNext = rowAfter;
         g = gNext;
         gNext = gAfter;

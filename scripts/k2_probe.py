@@ -17,7 +17,7 @@ def main():
     p.add_argument("--storage", default="uniform")
     p.add_argument("--rows", type=int, default=2_000_000)
     p.add_argument("--reps", type=int, default=20)
-    p.add_argument("--rows-kernel", type=int, default=1, help="0: element walk, 1: uniform_rows_kernel")
+    p.add_argument("--rows-kernel", type=int, default=1, help="0: element walk, 1: auto, 2: uniform_rows_kernel")
     a = p.parse_args()
     import torch
 

@@ -173,16 +173,16 @@ def test_uniform_parity(abi, oracle, synthetic, bits):
 
 @pytest.mark.parametrize("bits,dim", [(8, 8), (8, 12), (4, 300), (8, 300), (2, 1024), (8, 8188)])
 def test_uniform_rows_kernel_against_element_walk(abi, oracle, synthetic, bits, dim):
-    """Dense uniform lookups run through uniform_rows_kernel (per-row table in shared memory,
-    filled a 32-row group ahead); option uniform_rows_kernel = 0 sends the same call through the
-    element walk.  Both must equal the oracle bit for bit: ragged batches, one to many groups
+    """Dense uniform lookups run through uniform_rows_kernel (a warp per 32-row group, record
+    offsets in shared memory a group ahead) unless levels is a power of two; option
+    uniform_rows_kernel = 2 forces it, 0 sends the same call through the element walk.  Both must equal the oracle bit for bit: ragged batches, one to many groups
     per block, missing and out-of-range ids, sub-ranges."""
     rows = 700 if dim <= 1024 else 70
     syn = synthetic("uniform", bits, rows=rows, dim=dim, seed=60 + bits)
     reader, want = abi.open_checked(syn.path), oracle.open(syn.path)
     rng = np.random.default_rng(dim)
     table = want.decode_range(0, rows)
-    for option in (1, 0):
+    for option in (2, 1, 0):
         try:
             abi.check(abi.lib.memb_b200_set_option(b"uniform_rows_kernel", option))
             assert bits_equal(reader.decode_range(0, rows), table)
