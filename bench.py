@@ -646,7 +646,7 @@ def extra_configs(args, reader, device, peak):
         ms_ids = _time_launches(lambda: uni._impl.decode_ids_into(ids_u.data_ptr(), True, n, buf.data_ptr(), True, stream))
         ms_all = _time_launches(lambda: uni._impl.decode_range_into(0, rows_u, buf.data_ptr(), True, stream))
         out["uniform_%dbit" % bits] = {
-            "rows": rows_u, "kernel": "uniform_decode_kernel",
+            "rows": rows_u, "kernel": "uniform_decode_kernel" if bits in (1, 2, 4) else "uniform_rows_kernel",
             "random_ids": {"n": n, "ms": ms_ids, "rows_per_s": n / (ms_ids / 1e3),
                            "roofline_frac": n * (per_row + 4) / (ms_ids / 1e3) / 1e9 / peak},
             "full_vocab": {"ms": ms_all, "rows_per_s": rows_u / (ms_all / 1e3),
