@@ -51,6 +51,10 @@ def parse_args():
                    help="experiment: id distribution of the batch (the headline is `random`; misses5 = random "
                         "with 5 %% of the ids -1, i.e. out-of-vocabulary words)")
     p.add_argument("--trained-warps", type=int, default=0, help="experiment: cap resident warps per SM (0 = auto)")
+    p.add_argument("--quick", action="store_true",
+                   help="experiment: device-timed leg + a 20 k-row parity sample only (no e2e, no CPU baseline, no extras)")
+    p.add_argument("--option", action="append", default=[], metavar="NAME=VALUE",
+                   help="experiment: memb_b200_set_option before the table is opened (e.g. trained_rows_kernel=0)")
     p.add_argument("--cache-dir", default=os.environ.get("MEMB_B200_BENCH_DIR", "/tmp/memb_b200_bench"))
     return p.parse_args()
 
@@ -368,6 +372,9 @@ def run_b200(args):
 
     if args.trained_warps:
         _memb.set_option("trained_warps", args.trained_warps)
+    for item in args.option:
+        name, _, value = item.partition("=")
+        _memb.set_option(name, int(value))
     t0 = time.perf_counter()
     reader = memb_b200.Reader(table_path(args), device=local)
     open_s = time.perf_counter() - t0
@@ -401,6 +408,25 @@ def run_b200(args):
     ms_total = max_over_ranks(start.elapsed_time(stop))
     ms_step = ms_total / args.steps
     value = world * n / (ms_step / 1e3)
+
+    if args.quick:
+        if rank == 0:
+            oracle = CpuOracle(table_path(args), threads=0)
+            sample = ids_host.numpy()[:20000]
+            want = np.empty((len(sample), dim), np.float32)
+            oracle.batch_ids(sample, want)
+            step_device()
+            torch.cuda.synchronize()
+            ok = bool(np.array_equal(want.view(np.uint32), out_dev[:len(sample)].cpu().numpy().view(np.uint32)))
+            payload_per_row = stats["payload_bytes"] / rows
+            frac = n * (4 * dim + payload_per_row + 8) / (ms_step / 1e3) / 1e9 / measured_peak()[0]
+            print(json.dumps({"quick": True, "ids": args.ids, "options": args.option, "ms_per_step": ms_step,
+                              "rows_per_s": value, "roofline_frac": frac, "parity_sample": ok, "clocks": clocks,
+                              "gpu_launches": int(launches)}), file=_JSON_OUT, flush=True)
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
 
     # ---- e2e: the C-ABI call with HOST buffers (pinned), H2D ids + D2H rows inside the timed region ----
     with near_gpu(local):

@@ -105,6 +105,14 @@ memb_b200_status memb_b200_lookup_words(memb_b200_reader* reader, const char* qu
 memb_b200_status memb_b200_lookup_words_to(memb_b200_reader* reader, const char* query_bytes,
                                            const uint64_t* query_offsets, uint64_t n, float* out,
                                            memb_b200_mem_kind out_kind);
+/* The same into DEVICE memory with the caller's CUDA stream: the query upload, the resolve
+ * and the decode are queued on `stream` (0 = the legacy default stream), i.e. AFTER whatever
+ * the caller already queued there -- the ordering a stream-ordered allocator (torch's caching
+ * allocator) relies on when it hands out a block that earlier kernels of that stream still
+ * use.  Complete on return (the reader's query scratch is reused by the next call). */
+memb_b200_status memb_b200_lookup_words_on(memb_b200_reader* reader, const char* query_bytes,
+                                           const uint64_t* query_offsets, uint64_t n, float* out_device,
+                                           void* stream);
 
 /* The decode half of extract for n row ids — src/trained_compression.cpp:129-136,
  * src/uniform_compression.cpp:58-73, src/full_compression.cpp:41-42, plus the
@@ -132,6 +140,11 @@ memb_b200_status memb_b200_union_lookup_words_to(memb_b200_reader* const* reader
                                                  memb_b200_union_mode mode, const char* query_bytes,
                                                  const uint64_t* query_offsets, uint64_t n, float* out,
                                                  memb_b200_mem_kind out_kind);
+/* device output on the caller's stream: see memb_b200_lookup_words_on */
+memb_b200_status memb_b200_union_lookup_words_on(memb_b200_reader* const* readers, uint32_t num_readers,
+                                                 memb_b200_union_mode mode, const char* query_bytes,
+                                                 const uint64_t* query_offsets, uint64_t n, float* out_device,
+                                                 void* stream);
 memb_b200_status memb_b200_union_decode_ids(memb_b200_reader* const* readers, uint32_t num_readers,
                                             memb_b200_union_mode mode, const int32_t* ids,
                                             memb_b200_mem_kind ids_kind, uint64_t n, float* out,

@@ -446,15 +446,22 @@ public:
     }
 
     // additive: rows written to caller memory (torch data_ptr); returns the row count
-    uint64_t batchEmbeddingInto(const py::object& words, uintptr_t out, uint64_t capacityRows, bool outOnDevice) const
+    // (device output: queued on the caller's CUDA stream, memb_b200_lookup_words_on)
+    uint64_t batchEmbeddingInto(const py::object& words, uintptr_t out, uint64_t capacityRows, bool outOnDevice,
+                                uintptr_t stream) const
     {
         const auto m = marshal(words);
         if (m->n > capacityRows) {
             throw std::invalid_argument("batch_embedding_into: output holds fewer rows than words given");
         }
         py::gil_scoped_release release;
-        check(memb_b200_lookup_words_to(impl_, m->data, m->offsets, m->n, reinterpret_cast<float*>(out),
-                                        outOnDevice ? MEMB_B200_DEVICE : MEMB_B200_HOST));
+        if (outOnDevice) {
+            check(memb_b200_lookup_words_on(impl_, m->data, m->offsets, m->n, reinterpret_cast<float*>(out),
+                                            reinterpret_cast<void*>(stream)));
+        } else {
+            check(memb_b200_lookup_words_to(impl_, m->data, m->offsets, m->n, reinterpret_cast<float*>(out),
+                                            MEMB_B200_HOST));
+        }
         return m->n;
     }
 
@@ -595,7 +602,7 @@ py::array_t<float> unionBatchEmbedding(const std::vector<Reader*>& readers, cons
 }
 
 uint64_t unionBatchEmbeddingInto(const std::vector<Reader*>& readers, const std::string& mode, const py::object& words,
-                                 uintptr_t out, uint64_t capacityRows, bool outOnDevice)
+                                 uintptr_t out, uint64_t capacityRows, bool outOnDevice, uintptr_t stream)
 {
     UnionHandles u = unionHandles(readers, mode);
     const auto q = marshal(words);
@@ -603,9 +610,14 @@ uint64_t unionBatchEmbeddingInto(const std::vector<Reader*>& readers, const std:
         throw std::invalid_argument("union_batch_embedding_into: output holds fewer rows than words given");
     }
     py::gil_scoped_release release;
-    check(memb_b200_union_lookup_words_to(u.handles.data(), static_cast<uint32_t>(u.handles.size()), u.mode, q->data,
-                                          q->offsets, q->n, reinterpret_cast<float*>(out),
-                                          outOnDevice ? MEMB_B200_DEVICE : MEMB_B200_HOST));
+    if (outOnDevice) {
+        check(memb_b200_union_lookup_words_on(u.handles.data(), static_cast<uint32_t>(u.handles.size()), u.mode, q->data,
+                                              q->offsets, q->n, reinterpret_cast<float*>(out),
+                                              reinterpret_cast<void*>(stream)));
+    } else {
+        check(memb_b200_union_lookup_words_to(u.handles.data(), static_cast<uint32_t>(u.handles.size()), u.mode, q->data,
+                                              q->offsets, q->n, reinterpret_cast<float*>(out), MEMB_B200_HOST));
+    }
     return q->n;
 }
 
@@ -713,7 +725,7 @@ PYBIND11_MODULE(_memb, m)
         .def("resolve", &Reader::resolve)
         .def("batch_embedding_ids", &Reader::batchEmbeddingIds)
         .def("batch_embedding_into", &Reader::batchEmbeddingInto, py::arg("words"), py::arg("out"),
-             py::arg("capacity_rows"), py::arg("out_on_device"))
+             py::arg("capacity_rows"), py::arg("out_on_device"), py::arg("stream") = 0)
         .def_static("count_words", &Reader::countWords)
         .def("decode_range", &Reader::decodeRange)
         .def("decode_ids_into", &Reader::decodeIdsInto, py::arg("ids"), py::arg("ids_on_device"), py::arg("n"),
@@ -726,14 +738,17 @@ PYBIND11_MODULE(_memb, m)
     // additive
     m.def("union_batch_embedding", &unionBatchEmbedding);
     m.def("union_batch_embedding_into", &unionBatchEmbeddingInto, py::arg("readers"), py::arg("mode"), py::arg("words"),
-          py::arg("out"), py::arg("capacity_rows"), py::arg("out_on_device"));
+          py::arg("out"), py::arg("capacity_rows"), py::arg("out_on_device"), py::arg("stream") = 0);
     m.def("union_decode_ids_into", &unionDecodeIdsInto, py::arg("readers"), py::arg("mode"), py::arg("ids"),
           py::arg("ids_on_device"), py::arg("n"), py::arg("out"), py::arg("out_on_device"), py::arg("stream") = 0);
     // the marshalled form of a word collection: (UTF-8 bytes, uint64 offsets[n+1])
     m.def("pack_words", [](const py::object& words) {
         const auto q = marshal(words);
         py::array_t<uint64_t> offsets(static_cast<py::ssize_t>(q->n + 1));
-        std::memcpy(offsets.mutable_data(), q->offsets, (q->n + 1) * sizeof(uint64_t));
+        uint64_t* rebased = offsets.mutable_data();
+        for (size_t i = 0; i <= q->n; ++i) {
+            rebased[i] = q->offsets[i] - q->offsets[0];
+        }
         return py::make_tuple(py::bytes(q->data + q->offsets[0], q->offsets[q->n] - q->offsets[0]), offsets);
     });
     m.def("set_pinned_result_limit", [](uint64_t bytes) { PinnedResults::instance().setLimit(bytes); },

@@ -7,6 +7,7 @@
 #include "builder.h"
 #include "fb_format.h"
 #include "kernels.cuh"
+#include "trained_rows.cuh"
 #include "memb_file.h"
 
 #include <algorithm>
@@ -31,7 +32,10 @@ std::atomic<int64_t> g_optWarps{0};
 std::atomic<int64_t> g_optGeneric{0};
 std::atomic<int64_t> g_optPassRows{0};
 std::atomic<int64_t> g_optSymAverage{1};
-std::atomic<int64_t> g_optUniformRows{1};  // dense uniform lookups: 0 element walk, 1 uniform_rows_kernel unless levels is a power of two, 2 always
+std::atomic<int64_t> g_optUniformRows{1};
+std::atomic<int64_t> g_optTrainedRows{1};   // trained_rows_kernel: 0 never, 1 unions of trained readers (one launch), 2 single lookups too
+std::atomic<int64_t> g_optRowsWarps{0};     // cap on resident warps of trained_rows_kernel (0 = as many as fit)
+std::atomic<int64_t> g_optFixedRecords{1};  // 0: keep the offset table even when fixed-stride records would be cheap  // dense uniform lookups: 0 element walk, 1 uniform_rows_kernel unless levels is a power of two, 2 always
 
 struct StatusError {
     memb_b200_status status;
@@ -167,6 +171,17 @@ struct memb_b200_reader {
 
     // storage-specific
     K::TrainedParams trained{};
+    // trained_rows_kernel: LUT images of two widths ([0]: one reader, [1]: unions, half the shared memory)
+    struct RowsFlavour {
+        uint32_t lutBits = 0;
+        uint32_t lut2Entries = 0;
+        uint32_t* dImage = nullptr;
+        bool escape = false;
+    };
+    RowsFlavour rowsFlavour[2];
+    bool rowsOk = false;        // the table can go through trained_rows_kernel
+    uint32_t rowsFieldShift = 0, rowsZeroWord = 0;
+    uint32_t lut2Entries = 0;   // second-level entries of the ring kernel's LUT
     uint32_t trainedWarps = 0;  // 0 => generic kernel
     uint32_t trainedG = 4;
     bool trainedEscape = false;
@@ -199,34 +214,116 @@ struct memb_b200_reader {
 
 namespace {
 
-// Direct-table LUT over the next `lutBits` bits of the stream
-// (the GPU analogue of the table built in src/huffman_table_decoder.h:44-56;
-// fuzz in SURVEY §0 shows any table width decodes identically).  The decode
-// kernel holds its window LSB-first, so entry i is the code whose first bit is
-// bit 0 of i: the canonical (MSB-first) prefix with its bits reversed.
-// entry = (key << symShift) << 16 | escape << 15 | length.
-std::vector<uint32_t> buildLut(const PrefixCodeTable& code, uint32_t lutBits, uint32_t symShift)
+uint32_t reverseBits(uint32_t v, uint32_t width)
 {
-    const auto reversed = [lutBits](uint32_t prefix) {
-        uint32_t r = 0;
-        for (uint32_t b = 0; b < lutBits; ++b) {
-            r |= ((prefix >> b) & 1u) << (lutBits - 1 - b);
-        }
-        return r;
-    };
-    std::vector<uint32_t> lut(size_t(1) << lutBits, 0x8000u);
+    uint32_t r = 0;
+    for (uint32_t b = 0; b < width; ++b) {
+        r |= ((v >> b) & 1u) << (width - 1 - b);
+    }
+    return r;
+}
+
+// MSB-first direct table over L bits (the table of src/huffman_table_decoder.h:44-56):
+// direct[v] = index into code.keys of the code that prefixes the L-bit value v, or -1 when
+// that code is longer than L bits.
+std::vector<int> directTable(const PrefixCodeTable& code, uint32_t L)
+{
+    std::vector<int> direct(size_t(1) << L, -1);
     for (size_t i = 0; i < code.keys.size(); ++i) {
         const uint32_t len = code.lengths[i];
-        const uint32_t entry = ((static_cast<uint32_t>(code.keys[i]) << symShift) << 16) | len;
-        if (len <= lutBits) {
-            const uint32_t first = static_cast<uint32_t>(code.codes[i]) << (lutBits - len);
-            const uint32_t count = 1u << (lutBits - len);
-            for (uint32_t k = 0; k < count; ++k) {
-                lut[reversed(first + k)] = entry;
+        if (len <= L) {
+            const uint32_t first = static_cast<uint32_t>(code.codes[i]) << (L - len);
+            for (uint32_t k = 0; k < (1u << (L - len)); ++k) {
+                direct[first + k] = static_cast<int>(i);
             }
-        } else {
-            lut[reversed(code.codes[i] >> (len - lutBits))] = 0x8000u;  // escape: resolved bit-serially
         }
+    }
+    return direct;
+}
+
+// Second level for codes longer than L bits, the scheme of src/huffman_table_decoder.h:58-93:
+// one sub-table per distinct L-bit prefix of such codes, indexed by the NEXT `extra` stream
+// bits (first bit in bit 0, like the decoder's window), extra = longest code under the
+// prefix - L.  entryOf(i) is the table entry of code i.  Returns, per MSB-first prefix, the
+// escape description (base << 4 | extra), 0 for prefixes that need none.
+template <class EntryOf>
+std::vector<uint32_t> buildSecondLevel(const PrefixCodeTable& code, uint32_t L, EntryOf entryOf,
+                                       std::vector<uint32_t>& lut2)
+{
+    std::vector<uint32_t> extraOf(size_t(1) << L, 0), escape(size_t(1) << L, 0);
+    for (size_t i = 0; i < code.keys.size(); ++i) {
+        const uint32_t len = code.lengths[i];
+        if (len > L) {
+            const uint32_t prefix = code.codes[i] >> (len - L);
+            extraOf[prefix] = std::max(extraOf[prefix], len - L);
+        }
+    }
+    lut2.clear();
+    for (uint32_t prefix = 0; prefix < extraOf.size(); ++prefix) {
+        if (extraOf[prefix]) {
+            escape[prefix] = (static_cast<uint32_t>(lut2.size()) << 4) | extraOf[prefix];
+            lut2.resize(lut2.size() + (size_t(1) << extraOf[prefix]), 0);
+        }
+    }
+    for (size_t i = 0; i < code.keys.size(); ++i) {
+        const uint32_t len = code.lengths[i];
+        if (len > L) {
+            const uint32_t prefix = code.codes[i] >> (len - L);
+            const uint32_t extra = escape[prefix] & 15u, base = escape[prefix] >> 4;
+            const uint32_t rest = len - L;
+            const uint32_t tail = code.codes[i] & ((1u << rest) - 1u);
+            for (uint32_t k = 0; k < (1u << (extra - rest)); ++k) {
+                lut2[base + reverseBits((tail << (extra - rest)) | k, extra)] = entryOf(i);
+            }
+        }
+    }
+    return escape;
+}
+
+// LUT of the ring kernel (trained_decode_kernel) over the next `lutBits` bits of the stream.
+// The decode kernels hold their window LSB-first, so entry i is the code whose first bit is
+// bit 0 of i: the canonical (MSB-first) prefix with its bits reversed.
+// entry = (key << symShift) << 16 | length; a code longer than the LUT is wide:
+// 0x8000 | extra | base << 16 -> lut2[base + next `extra` bits] holds the entry.
+std::vector<uint32_t> buildLut(const PrefixCodeTable& code, uint32_t lutBits, uint32_t symShift,
+                               std::vector<uint32_t>& lut2)
+{
+    const auto entryOf = [&](size_t i) {
+        return ((static_cast<uint32_t>(code.keys[i]) << symShift) << 16) | code.lengths[i];
+    };
+    const std::vector<int> direct = directTable(code, lutBits);
+    const std::vector<uint32_t> escape = buildSecondLevel(code, lutBits, entryOf, lut2);
+    std::vector<uint32_t> lut(size_t(1) << lutBits, 0);
+    for (uint32_t v = 0; v < lut.size(); ++v) {
+        lut[reverseBits(v, lutBits)] =
+            direct[v] >= 0 ? entryOf(direct[v]) : (0x8000u | (escape[v] & 15u) | ((escape[v] >> 4) << 16));
+    }
+    return lut;
+}
+
+// Multi-symbol LUT of trained_rows_kernel (entry format: trained_rows.cuh): entry i decodes,
+// greedily, up to three whole codes out of the L stream bits i (first bit = bit 0).
+std::vector<uint32_t> buildRowsLut(const PrefixCodeTable& code, uint32_t L, uint32_t symShift,
+                                   std::vector<uint32_t>& lut2)
+{
+    const std::vector<int> direct = directTable(code, L);
+    const std::vector<uint32_t> escape = buildSecondLevel(
+        code, L,
+        [&](size_t i) { return ((static_cast<uint32_t>(code.keys[i]) << symShift) << 8) | (1u << 5) | code.lengths[i]; }, lut2);
+    std::vector<uint32_t> lut(size_t(1) << L, 0);
+    const uint32_t mask = (1u << L) - 1u;
+    for (uint32_t v = 0; v <= mask; ++v) {
+        uint32_t pos = 0, count = 0, syms = 0;
+        while (count < 3) {
+            const int k = direct[(v << pos) & mask];  // the remaining bits, left-aligned, zero-filled
+            if (k < 0 || pos + code.lengths[k] > L) {
+                break;
+            }
+            syms |= (static_cast<uint32_t>(code.keys[k]) << symShift) << (8 * count);
+            pos += code.lengths[k];
+            ++count;
+        }
+        lut[reverseBits(v, L)] = count ? (syms << 8) | (count << 5) | pos : ((escape[v] >> 4) << 12) | ((escape[v] & 15u) << 8);
     }
     return lut;
 }
@@ -303,25 +400,27 @@ void loadTrained(memb_b200_reader& r)
     r.stats.upload_ms += msSince(t0);
 
     const auto t1 = std::chrono::steady_clock::now();
-    // decode tables first: the LUT flavour fixes how the rows are re-packed
+    // decode tables first: the LUT flavour fixes how the rows are re-packed.  Default: one LUT
+    // copy per shared-memory bank over min(maxLen, 9) bits, longer codes through a second-level
+    // table (src/huffman_table_decoder.h:58-93).  Option trained_lut_replicas = 1 (tests): a
+    // single copy over up to 12 bits.
     const uint32_t maxLen = f.code.maxLen;
-    int64_t replicasOpt = g_optLutReplicas.load();
     uint32_t replicas, lutBits, padBits;
-    if (replicasOpt == 32 || (replicasOpt == 0 && maxLen <= 9)) {
-        replicas = 32;  // one copy per shared-memory bank, entry i of lane l at i*128 + l*4
-        lutBits = std::max(1u, std::min(maxLen, 9u));
-        padBits = 7;
-    } else {
+    if (g_optLutReplicas.load() == 1) {
         replicas = 1;
         lutBits = std::max(1u, std::min(maxLen, 12u));
         padBits = 2;
+    } else {
+        replicas = 32;  // entry i of lane l at i*128 + l*4
+        lutBits = std::max(1u, std::min(maxLen, 9u));
+        padBits = K::ROWS_PAD_BITS;
     }
     const bool escape = maxLen > lutBits;
     const uint32_t codebookSize = static_cast<uint32_t>(f.centroids.size());
     // <= 64 centroids: the symbol field carries sym * 4, the byte offset into the codebook
     const uint32_t symShift = (!escape && codebookSize <= 64) ? 2u : 0u;
 
-    // exact row lengths -> offsets of the 16 B-aligned re-pack
+    // exact row lengths -> 16 B-aligned re-pack
     uint32_t* dRowBytes = nullptr;
     CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&dRowBytes), std::max<size_t>(size_t(rows) * 4, 16)));
     if (rows) {
@@ -333,49 +432,82 @@ void loadTrained(memb_b200_reader& r)
     std::vector<uint32_t> rowBytes(rows);
     CUDA_CHECK(cudaMemcpyAsync(rowBytes.data(), dRowBytes, size_t(rows) * 4, cudaMemcpyDeviceToHost, r.stream));
     CUDA_CHECK(cudaStreamSynchronize(r.stream));
-    std::vector<uint32_t> rowOff16(size_t(rows) + 1);
-    uint64_t units = 0, payload = 0;
+    // padBits (< 8) extra bits in front of the row: one more byte
+    const auto unitsOf = [](uint32_t bytes) {
+        return bytes ? (bytes + 1 + K::TRAINED_UNIT_BYTES - 1) / K::TRAINED_UNIT_BYTES : 0u;
+    };
+    uint64_t sumUnits = 0, payload = 0;
     uint32_t maxRowUnits = 0;
     for (uint32_t i = 0; i < rows; ++i) {
-        rowOff16[i] = static_cast<uint32_t>(units);
-        // padBits (< 8) extra bits in front of the row: one more byte
-        const uint32_t rowUnits = rowBytes[i] ? (rowBytes[i] + 1 + K::TRAINED_UNIT_BYTES - 1) / K::TRAINED_UNIT_BYTES : 0;
-        units += rowUnits;
+        sumUnits += unitsOf(rowBytes[i]);
         payload += rowBytes[i];
-        maxRowUnits = std::max(maxRowUnits, rowUnits);
-        if (units > 0xffffffffULL) {
-            fail(MEMB_B200_ERR_FORMAT, "memb file: re-packed rows exceed 64 GiB");
-        }
+        maxRowUnits = std::max(maxRowUnits, unitsOf(rowBytes[i]));
     }
-    rowOff16[rows] = static_cast<uint32_t>(units);
     r.stats.payload_bytes = payload;
-    uint32_t* dRowOff16 = deviceUpload(rowOff16.data(), rowOff16.size(), r.stats.device_bytes);
-    r.owned.push_back(dRowOff16);
+    // Fixed-stride RECORDS when the longest row is close to the average one (rows of a
+    // k-means + Huffman table are: 131 +- 2 B at 4 bits): row r at r * recUnits, no offset
+    // table -- a lookup is id -> record instead of id -> offset -> row, and the 4 B gather
+    // that cost a 64 B DRAM access per row is gone.  Otherwise rows back to back + offsets.
+    const uint32_t recUnits = std::max(maxRowUnits, 1u);
+    const bool fixed = g_optFixedRecords.load() && uint64_t(rows) * recUnits <= sumUnits + sumUnits / 4 + 4096;
+    std::vector<uint32_t> rowOff16;
+    uint64_t units = fixed ? uint64_t(std::max(rows, 1u)) * recUnits : 0;
+    if (!fixed) {
+        rowOff16.resize(size_t(rows) + 1);
+        for (uint32_t i = 0; i < rows; ++i) {
+            rowOff16[i] = static_cast<uint32_t>(units);
+            units += unitsOf(rowBytes[i]);
+            if (units > 0xffffffffULL) {
+                fail(MEMB_B200_ERR_FORMAT, "memb file: re-packed rows exceed 64 GiB");
+            }
+        }
+        rowOff16[rows] = static_cast<uint32_t>(units);
+    } else if (units > 0xffffffffULL) {
+        fail(MEMB_B200_ERR_FORMAT, "memb file: re-packed rows exceed 64 GiB");
+    }
+    uint32_t* dRowOff16 = nullptr;
+    if (!fixed) {
+        dRowOff16 = deviceUpload(rowOff16.data(), rowOff16.size(), r.stats.device_bytes);
+        r.owned.push_back(dRowOff16);
+    }
     K::RowUnit* dBlob = nullptr;
     // one spare unit so the decoder's 96-bit window never leaves the allocation
     const size_t blobBytes = (units + 1) * K::TRAINED_UNIT_BYTES;
     CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&dBlob), blobBytes));
     r.stats.device_bytes += blobBytes;
     r.owned.push_back(dBlob);
+    if (rows == 0) {
+        // a table without rows still has record 0: lanes without a row decode it
+        CUDA_CHECK(cudaMemsetAsync(dBlob, 0, blobBytes, r.stream));
+    }
     CUDA_CHECK(cudaMemsetAsync(reinterpret_cast<unsigned char*>(dBlob) + units * K::TRAINED_UNIT_BYTES, 0,
                                K::TRAINED_UNIT_BYTES, r.stream));
     if (rows) {
         const uint64_t threads = uint64_t(rows) * 32;
         K::repack_rows_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, r.stream>>>(
-            dPacked, f.packedSize, dValueOffsets, dRowBytes, dRowOff16, rows, padBits,
+            dPacked, f.packedSize, dValueOffsets, dRowBytes, dRowOff16, fixed ? recUnits : 0u, rows, padBits,
             reinterpret_cast<uint32_t*>(dBlob));
         ++g_launches;
         CUDA_CHECK(cudaGetLastError());
     }
 
-    const std::vector<uint32_t> lut = buildLut(f.code, lutBits, symShift);
+    std::vector<uint32_t> lut2;
+    const std::vector<uint32_t> lut = buildLut(f.code, lutBits, symShift, lut2);
+    if (lut2.size() > K::ROWS_LUT2_MAX_ENTRIES) {
+        fail(MEMB_B200_ERR_UNSUPPORTED, "memb file: prefix code needs more second-level table entries than the kernels hold");
+    }
     uint32_t* dLut = deviceUpload(lut.data(), lut.size(), r.stats.device_bytes);
     r.owned.push_back(dLut);
+    uint32_t* dLut2 = deviceUpload(lut2.data(), lut2.size(), r.stats.device_bytes);
+    r.owned.push_back(dLut2);
 
     K::TrainedParams& p = r.trained;
     p.blob = dBlob;
     p.rowOff16 = dRowOff16;
+    p.recUnits = fixed ? recUnits : 0u;
     p.lut = dLut;
+    p.lut2 = dLut2;
+    p.lut2Entries = static_cast<uint32_t>(lut2.size());
     p.codebook = dCodebook;
     p.code = dCode;
     p.rows = rows;
@@ -396,13 +528,46 @@ void loadTrained(memb_b200_reader& r)
     const uint32_t allowed = (64 - padBits) / std::max(maxLen, 1u);
     r.trainedG = escape ? 3 : allowed >= 16 ? 16 : allowed >= 8 ? 8 : allowed >= 7 ? 7 : allowed >= 6 ? 6 : 5;
 
+    // ---- trained_rows_kernel: multi-symbol LUT images, 9 bits wide for one reader, 8 for unions ----
+    r.rowsOk = false;
+    if (fixed && padBits == K::ROWS_PAD_BITS && codebookSize <= 255 && f.dim % 4 == 0 && f.dim >= 4 &&
+        f.dim <= K::TRAINED_MAX_DIM) {
+        r.rowsFieldShift = codebookSize <= 63 ? 0u : 2u;  // <= 63 centroids: the field already is sym * 4
+        const uint32_t rowsSymShift = 2u - r.rowsFieldShift;
+        r.rowsZeroWord = ((codebookSize << rowsSymShift) & 0xffu) * 0x01010101u;
+        r.rowsOk = true;
+        for (int flavour = 0; flavour < 2 && r.rowsOk; ++flavour) {
+            const uint32_t L = std::max(1u, std::min(maxLen * 3u, flavour == 0 ? 9u : 8u));
+            std::vector<uint32_t> rowsLut2;
+            const std::vector<uint32_t> rowsLut = buildRowsLut(f.code, L, rowsSymShift, rowsLut2);
+            if (rowsLut2.size() > K::ROWS_LUT2_MAX_ENTRIES) {
+                r.rowsOk = false;
+                break;
+            }
+            rowsLut2.resize((rowsLut2.size() + 3) / 4 * 4, 0);
+            // image: LUT with 32 bank replicas | second level | 256 codebook floats (zero padded)
+            std::vector<uint32_t> image((size_t(32) << L) + rowsLut2.size() + 256, 0);
+            for (size_t i = 0; i < rowsLut.size(); ++i) {
+                std::fill_n(image.begin() + i * 32, 32, rowsLut[i]);
+            }
+            std::copy(rowsLut2.begin(), rowsLut2.end(), image.begin() + (size_t(32) << L));
+            std::memcpy(image.data() + (size_t(32) << L) + rowsLut2.size(), f.centroids.data(), codebookSize * 4);
+            memb_b200_reader::RowsFlavour& fl = r.rowsFlavour[flavour];
+            fl.lutBits = L;
+            fl.lut2Entries = static_cast<uint32_t>(rowsLut2.size());
+            fl.escape = maxLen > L;
+            fl.dImage = deviceUpload(image.data(), image.size(), r.stats.device_bytes);
+            r.owned.push_back(fl.dImage);
+        }
+    }
+
     // how many warps (tiles in flight) fit beside the tables in the shared window
     r.smemBase = probeSmemBase(r.stream);
     const uint32_t lutBytes = K::trainedLutBytes(lutBits, replicas);
     const uint32_t perWarp = K::trainedWarpBytes(p.rowWords);
     uint32_t warps = 0;
     for (uint32_t w = 1; w <= K::TRAINED_MAX_WARPS; ++w) {
-        const K::TrainedLayout lay = K::trainedLayout(r.smemBase, lutBytes, perWarp, w);
+        const K::TrainedLayout lay = K::trainedLayout(r.smemBase, lutBytes, perWarp, w, p.lut2Entries);
         if (lay.end - r.smemBase > r.smemOptin) {
             break;
         }
@@ -514,7 +679,7 @@ void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t
 {
     const K::TrainedParams& p = r.trained;
     const K::TrainedLayout lay = K::trainedLayout(r.smemBase, K::trainedLutBytes(p.lutBits, p.lutReplicas),
-                                                  K::trainedWarpBytes(p.rowWords), r.trainedWarps);
+                                                  K::trainedWarpBytes(p.rowWords), r.trainedWarps, p.lut2Entries);
     const size_t smemBytes = lay.end - r.smemBase;
     const uint64_t tiles = (n + 31) / 32;
     const unsigned grid = static_cast<unsigned>(
@@ -528,6 +693,198 @@ void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t
     uint32_t* counter = r.dTileCounters + (const_cast<memb_b200_reader&>(r).launchSeq++ % memb_b200_reader::TILE_COUNTERS);
     CUDA_CHECK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), stream));
     kernel<<<grid, block, smemBytes, stream>>>(p, ids, rowBegin, n, o, epi, counter);
+}
+
+// ---- trained_rows_kernel: shared-window plan and launch ----
+struct RowsPlan {
+    K::RowsParams P{};
+    uint32_t warps = 0;
+    size_t smemBytes = 0;
+    int G = 6;
+    bool escape = false;
+    bool smallCodebooks = true;
+};
+
+// First-fit allocator over the free fragments of the CTA's shared window.
+struct SmemFragments {
+    std::vector<std::pair<uint32_t, uint32_t>> free;  // [begin, end)
+    uint32_t highWater = 0;
+    uint32_t alloc(uint32_t bytes, uint32_t align)
+    {
+        for (auto& f : free) {
+            const uint32_t at = (f.first + align - 1) / align * align;
+            if (at + bytes <= f.second) {
+                f.first = at + bytes;  // (the alignment gap is lost: blocks only grow in size order)
+                highWater = std::max(highWater, at + bytes);
+                return at;
+            }
+        }
+        return 0;
+    }
+};
+
+// Lays R readers out in the shared window: LUT images at addresses aligned to their own size
+// (the decode ORs base, bank replica and index together), small tables and the per-warp
+// blocks (staged records, symbol tiles) first-fit into the fragments around them.
+// Returns false when the union cannot run as one launch (then the ring kernels take it).
+bool planRows(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_mode mode, RowsPlan& plan)
+{
+    const int64_t use = g_optTrainedRows.load();
+    if (R == 0 || R > 2 || use == 0 || (R == 1 && use < 2)) {
+        return false;  // instantiated for one and two readers
+    }
+    const memb_b200_reader& r0 = *readers[0];
+    const int flavour = R == 1 ? 0 : 1;
+    K::RowsParams& P = plan.P;
+    uint32_t maxLen = 0, colWords = 0, outUnits = 0, tileBytes = 0;
+    for (uint32_t k = 0; k < R; ++k) {
+        const memb_b200_reader& r = *readers[k];
+        if (r.file->storage != STORAGE_TRAINED || !r.rowsOk || r.device != r0.device) {
+            return false;
+        }
+        const auto& fl = r.rowsFlavour[flavour];
+        K::RowsReader& rd = P.rd[k];
+        rd.blob = r.trained.blob;
+        rd.lutImage = fl.dImage;
+        rd.recUnits = r.trained.recUnits;
+        rd.rows = r.trained.rows;
+        rd.dim = r.trained.dim;
+        rd.lutBits = fl.lutBits;
+        rd.lut2Entries = fl.lut2Entries;
+        rd.zeroWord = r.rowsZeroWord;
+        rd.fieldShift = r.rowsFieldShift;
+        const uint32_t words = rd.dim / 4;
+        rd.tileStride = (words | 1u) * 4;  // odd number of words: lanes writing the same word of their rows hit 32 banks
+        rd.tileOffset = tileBytes;
+        tileBytes += 32 * rd.tileStride;
+        rd.colUnit = mode == MEMB_B200_CONCATENATE ? outUnits : 0;
+        outUnits = mode == MEMB_B200_CONCATENATE ? outUnits + words : words;
+        colWords = std::max(colWords, rd.recUnits * K::TRAINED_UNIT_WORDS + 4);
+        plan.escape = plan.escape || fl.escape;
+        plan.smallCodebooks = plan.smallCodebooks && rd.fieldShift == 0;
+        maxLen = std::max(maxLen, r.file->code.maxLen);
+    }
+    // lookups per window reload: every lookup consumes (and peeks) at most max(L, maxLen) bits
+    plan.G = !plan.escape ? 6 : maxLen <= 13 ? 4 : 3;
+    P.colWords = colWords;
+    P.outUnits = outUnits;
+    P.divisor = static_cast<float>(R);
+
+    const uint32_t base = r0.smemBase, limit = base + static_cast<uint32_t>(r0.smemOptin);
+    // LUTs, largest first, back to back from the first address aligned to the largest
+    std::vector<uint32_t> order(R);
+    for (uint32_t k = 0; k < R; ++k) {
+        order[k] = k;
+    }
+    std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return P.rd[a].lutBits > P.rd[b].lutBits; });
+    const uint32_t firstBytes = 128u << P.rd[order[0]].lutBits;
+    uint32_t cursor = (base + firstBytes) / firstBytes * firstBytes;
+    const uint32_t lutBegin = cursor;
+    for (uint32_t k : order) {
+        P.rd[k].sLut = cursor;  // sizes are powers of two in descending order: still aligned
+        cursor += 128u << P.rd[k].lutBits;
+    }
+    if (cursor > limit) {
+        return false;
+    }
+    SmemFragments frag;
+    frag.free = {{base, lutBegin}, {cursor, limit}};
+    frag.highWater = cursor;
+    P.sMbar = frag.alloc(8, 8);
+    for (uint32_t k = 0; k < R; ++k) {
+        P.rd[k].sCodebook = frag.alloc(1024, 1024);
+        P.rd[k].sLut2 = P.rd[k].lut2Entries ? frag.alloc(P.rd[k].lut2Entries * 4, 16) : P.sMbar;
+        if (!P.rd[k].sCodebook || !P.rd[k].sLut2) {
+            return false;
+        }
+    }
+    const int64_t cap = g_optRowsWarps.load();
+    const uint32_t maxWarps = cap > 0 ? std::min<uint32_t>(K::ROWS_MAX_WARPS, static_cast<uint32_t>(cap)) : K::ROWS_MAX_WARPS;
+    uint32_t warps = 0;
+    // tiles first (the larger blocks), then the staging columns
+    for (; warps < maxWarps; ++warps) {
+        const SmemFragments saved = frag;
+        const uint32_t tile = frag.alloc(tileBytes, 16);
+        const uint32_t cols = tile ? frag.alloc(colWords * 128, 128) : 0;
+        if (!tile || !cols) {
+            frag = saved;
+            break;
+        }
+        P.sTiles[warps] = tile;
+        P.sCols[warps] = cols;
+    }
+    if (warps < 4 || !P.sMbar) {
+        return false;
+    }
+    plan.warps = warps;
+    P.smemEnd = frag.highWater;
+    plan.smemBytes = frag.highWater - base;
+    return true;
+}
+
+template <int R, int MODE, int G, bool ESC, bool SMALLCB>
+void launchRowsKernel(const memb_b200_reader& r0, const RowsPlan& plan, const int32_t* ids, uint64_t idStride,
+                      uint32_t rowBegin, uint64_t n, float* out, cudaStream_t stream)
+{
+    auto kernel = K::trained_rows_kernel<R, MODE, G, ESC, SMALLCB>;
+    // once per instantiation and device: the opt-in maximum (not this launch's size, which
+    // another thread's launch of the same instantiation could undercut)
+    static std::atomic<uint64_t> configured{0};
+    const uint64_t bit = 1ull << (r0.device & 63);
+    if (!(configured.load() & bit)) {
+        CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(r0.smemOptin)));
+        configured |= bit;
+    }
+    const uint64_t tiles = (n + 31) / 32;
+    const unsigned grid = static_cast<unsigned>(
+        std::min<uint64_t>(static_cast<uint64_t>(r0.numSMs), (tiles + plan.warps - 1) / plan.warps));
+    if (tiles + 4ull * grid * plan.warps >= 0xffffffffull) {
+        fail(MEMB_B200_ERR_ARGUMENT, "decode: too many rows in one call");
+    }
+    uint32_t* counter = r0.dTileCounters + (const_cast<memb_b200_reader&>(r0).launchSeq++ % memb_b200_reader::TILE_COUNTERS);
+    CUDA_CHECK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), stream));
+    kernel<<<grid, plan.warps * 32, plan.smemBytes, stream>>>(plan.P, ids, idStride, rowBegin, n, out, counter);
+    ++g_launches;
+    CUDA_CHECK(cudaGetLastError());
+}
+
+template <int R, int MODE>
+void launchRowsFlavour(const memb_b200_reader& r0, const RowsPlan& plan, const int32_t* ids, uint64_t idStride,
+                       uint32_t rowBegin, uint64_t n, float* out, cudaStream_t stream)
+{
+    const bool s = plan.smallCodebooks;
+    if (!plan.escape) {
+        s ? launchRowsKernel<R, MODE, 6, false, true>(r0, plan, ids, idStride, rowBegin, n, out, stream)
+          : launchRowsKernel<R, MODE, 6, false, false>(r0, plan, ids, idStride, rowBegin, n, out, stream);
+    } else if (plan.G == 4) {
+        s ? launchRowsKernel<R, MODE, 4, true, true>(r0, plan, ids, idStride, rowBegin, n, out, stream)
+          : launchRowsKernel<R, MODE, 4, true, false>(r0, plan, ids, idStride, rowBegin, n, out, stream);
+    } else {
+        s ? launchRowsKernel<R, MODE, 3, true, true>(r0, plan, ids, idStride, rowBegin, n, out, stream)
+          : launchRowsKernel<R, MODE, 3, true, false>(r0, plan, ids, idStride, rowBegin, n, out, stream);
+    }
+}
+
+// One launch for a dense (n x union dim) result of trained readers; false: not applicable.
+bool tryLaunchRows(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_mode mode, const int32_t* ids,
+                   uint64_t idStride, uint32_t rowBegin, uint64_t n, float* out, cudaStream_t stream)
+{
+    if (n == 0 || reinterpret_cast<uintptr_t>(out) % 16 != 0) {
+        return false;
+    }
+    RowsPlan plan;
+    if (!planRows(readers, R, mode, plan)) {
+        return false;
+    }
+    const memb_b200_reader& r0 = *readers[0];
+    if (R == 1) {
+        launchRowsFlavour<1, K::ROWS_CONCAT>(r0, plan, ids, idStride, rowBegin, n, out, stream);
+    } else if (mode == MEMB_B200_AVERAGE) {
+        launchRowsFlavour<2, K::ROWS_AVERAGE>(r0, plan, ids, idStride, rowBegin, n, out, stream);
+    } else {
+        launchRowsFlavour<2, K::ROWS_CONCAT>(r0, plan, ids, idStride, rowBegin, n, out, stream);
+    }
+    return true;
 }
 
 // Picks the instantiation: G symbols per window reload (loadTrained); for the
@@ -614,6 +971,13 @@ void launchDecode(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBeg
     const unsigned flatGrid = static_cast<unsigned>(std::min<uint64_t>((elems + 255) / 256, uint64_t(r.numSMs) * 32));
     switch (r.file->storage) {
     case STORAGE_TRAINED:
+        if (vec && epi == K::EPI_WRITE && o.rowStride == dim && o.colOffset == 0 && !o.sideHead && !o.sideTail && !o.sym) {
+            // dense result of a plain lookup: whole rows, contiguous flush (trained_rows.cuh)
+            memb_b200_reader* self = const_cast<memb_b200_reader*>(&r);
+            if (tryLaunchRows(&self, 1, MEMB_B200_CONCATENATE, ids, 0, rowBegin, n, o.out, stream)) {
+                return;
+            }
+        }
         if (r.trainedWarps == 0) {
             const unsigned grid = static_cast<unsigned>((n + 127) / 128);
             if (epi == K::EPI_WRITE) {
@@ -731,6 +1095,10 @@ bool canRedirectUnits(const memb_b200_reader& r, const K::OutputSpec& o)
 void launchUnion(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_mode mode, const int32_t* dIds,
                  uint64_t idStride, uint64_t first, uint64_t n, float* dOut, uint64_t unionDim, cudaStream_t stream)
 {
+    // trained readers: the whole union in ONE launch (trained_rows.cuh)
+    if (tryLaunchRows(readers, R, mode, dIds + first, idStride, 0, n, dOut, stream)) {
+        return;
+    }
     std::vector<K::OutputSpec> specs(R);
     uint32_t col = 0;
     for (uint32_t k = 0; k < R; ++k) {
@@ -872,6 +1240,12 @@ memb_b200_status memb_b200_set_option(const char* name, int64_t value)
             g_optSymAverage = value;
         } else if (key == "uniform_rows_kernel" && value >= 0 && value <= 2) {
             g_optUniformRows = value;
+        } else if (key == "trained_rows_kernel" && value >= 0 && value <= 2) {
+            g_optTrainedRows = value;
+        } else if (key == "trained_rows_warps" && value >= 0 && value <= K::ROWS_MAX_WARPS) {
+            g_optRowsWarps = value;
+        } else if (key == "trained_fixed_records" && (value == 0 || value == 1)) {
+            g_optFixedRecords = value;
         } else if (key == "host_pass_rows" && value >= 0) {
             g_optPassRows = value;  // rows staged per pass for host outputs (0 = 4 GiB of fp32)
         } else {
@@ -1116,9 +1490,9 @@ memb_b200_status memb_b200_resolve(memb_b200_reader* reader, const char* query_b
     });
 }
 
-memb_b200_status memb_b200_lookup_words_to(memb_b200_reader* reader, const char* query_bytes,
-                                           const uint64_t* query_offsets, uint64_t n, float* out,
-                                           memb_b200_mem_kind out_kind)
+static memb_b200_status lookupWords(memb_b200_reader* reader, const char* query_bytes, const uint64_t* query_offsets,
+                                    uint64_t n, float* out, memb_b200_mem_kind out_kind, bool callerStream,
+                                    void* stream)
 {
     return guarded([&] {
         if (!reader) {
@@ -1127,15 +1501,29 @@ memb_b200_status memb_b200_lookup_words_to(memb_b200_reader* reader, const char*
         DeviceGuard guard(reader->device);
         std::lock_guard<std::mutex> lock(reader->mutex);
         memb_b200_reader& r = *reader;
-        const int32_t* dIds = resolveToDevice(r, query_bytes, query_offsets, n, r.stream);
+        cudaStream_t s = callerStream ? static_cast<cudaStream_t>(stream) : r.stream;
+        const int32_t* dIds = resolveToDevice(r, query_bytes, query_offsets, n, s);
         const uint32_t dim = r.file->dim;
-        decodeTo(r, n, dim, out, out_kind, r.stream, [&](uint64_t first, uint64_t count, float* dOut) {
+        decodeTo(r, n, dim, out, out_kind, s, [&](uint64_t first, uint64_t count, float* dOut) {
             K::OutputSpec o{dOut, dim, 0, 1.0f};
-            launchDecode(r, dIds + first, 0, count, o, K::EPI_WRITE, r.stream);
+            launchDecode(r, dIds + first, 0, count, o, K::EPI_WRITE, s);
         });
         // the scratch ids/query buffers are reused by the next call: finish before returning
-        CUDA_CHECK(cudaStreamSynchronize(r.stream));
+        CUDA_CHECK(cudaStreamSynchronize(s));
     });
+}
+
+memb_b200_status memb_b200_lookup_words_to(memb_b200_reader* reader, const char* query_bytes,
+                                           const uint64_t* query_offsets, uint64_t n, float* out,
+                                           memb_b200_mem_kind out_kind)
+{
+    return lookupWords(reader, query_bytes, query_offsets, n, out, out_kind, false, nullptr);
+}
+
+memb_b200_status memb_b200_lookup_words_on(memb_b200_reader* reader, const char* query_bytes,
+                                           const uint64_t* query_offsets, uint64_t n, float* out_device, void* stream)
+{
+    return lookupWords(reader, query_bytes, query_offsets, n, out_device, MEMB_B200_DEVICE, true, stream);
 }
 
 memb_b200_status memb_b200_lookup_words(memb_b200_reader* reader, const char* query_bytes,
@@ -1228,10 +1616,10 @@ memb_b200_status memb_b200_union_decode_ids(memb_b200_reader* const* readers, ui
     });
 }
 
-memb_b200_status memb_b200_union_lookup_words_to(memb_b200_reader* const* readers, uint32_t num_readers,
-                                                 memb_b200_union_mode mode, const char* query_bytes,
-                                                 const uint64_t* query_offsets, uint64_t n, float* out,
-                                                 memb_b200_mem_kind out_kind)
+static memb_b200_status unionLookupWords(memb_b200_reader* const* readers, uint32_t num_readers,
+                                         memb_b200_union_mode mode, const char* query_bytes,
+                                         const uint64_t* query_offsets, uint64_t n, float* out,
+                                         memb_b200_mem_kind out_kind, bool callerStream, void* stream)
 {
     return guarded([&] {
         if (!readers) {
@@ -1247,23 +1635,40 @@ memb_b200_status memb_b200_union_lookup_words_to(memb_b200_reader* const* reader
         if (!query_bytes || !query_offsets) {
             fail(MEMB_B200_ERR_ARGUMENT, "null query buffer");
         }
+        cudaStream_t s = callerStream ? static_cast<cudaStream_t>(stream) : r.stream;
         // one upload of the query text, one resolve per reader (each has its own vocabulary)
         const uint64_t base = query_offsets[0];
         const uint64_t bytes = query_offsets[n] - base;
         char* dQuery = static_cast<char*>(r.scratchQuery.ensure(std::max<uint64_t>(bytes, 1)));
         uint64_t* dOffsets = static_cast<uint64_t*>(r.scratchOffsets.ensure((n + 1) * 8));
         int32_t* dIds = static_cast<int32_t*>(r.scratchIds.ensure(n * num_readers * 4));
-        CUDA_CHECK(cudaMemcpyAsync(dQuery, query_bytes + base, bytes, cudaMemcpyHostToDevice, r.stream));
-        CUDA_CHECK(cudaMemcpyAsync(dOffsets, query_offsets, (n + 1) * 8, cudaMemcpyHostToDevice, r.stream));
+        CUDA_CHECK(cudaMemcpyAsync(dQuery, query_bytes + base, bytes, cudaMemcpyHostToDevice, s));
+        CUDA_CHECK(cudaMemcpyAsync(dOffsets, query_offsets, (n + 1) * 8, cudaMemcpyHostToDevice, s));
         for (uint32_t k = 0; k < num_readers; ++k) {
-            launchResolve(*readers[k], dQuery - base, dOffsets, n, dIds + k * n, r.stream);
+            launchResolve(*readers[k], dQuery - base, dOffsets, n, dIds + k * n, s);
         }
-        decodeTo(r, n, unionDim, out, out_kind, r.stream,
-                 [&](uint64_t first, uint64_t count, float* dOut) {
-                     launchUnion(readers, num_readers, mode, dIds, n, first, count, dOut, unionDim, r.stream);
-                 });
-        CUDA_CHECK(cudaStreamSynchronize(r.stream));
+        decodeTo(r, n, unionDim, out, out_kind, s, [&](uint64_t first, uint64_t count, float* dOut) {
+            launchUnion(readers, num_readers, mode, dIds, n, first, count, dOut, unionDim, s);
+        });
+        CUDA_CHECK(cudaStreamSynchronize(s));
     });
+}
+
+memb_b200_status memb_b200_union_lookup_words_to(memb_b200_reader* const* readers, uint32_t num_readers,
+                                                 memb_b200_union_mode mode, const char* query_bytes,
+                                                 const uint64_t* query_offsets, uint64_t n, float* out,
+                                                 memb_b200_mem_kind out_kind)
+{
+    return unionLookupWords(readers, num_readers, mode, query_bytes, query_offsets, n, out, out_kind, false, nullptr);
+}
+
+memb_b200_status memb_b200_union_lookup_words_on(memb_b200_reader* const* readers, uint32_t num_readers,
+                                                 memb_b200_union_mode mode, const char* query_bytes,
+                                                 const uint64_t* query_offsets, uint64_t n, float* out_device,
+                                                 void* stream)
+{
+    return unionLookupWords(readers, num_readers, mode, query_bytes, query_offsets, n, out_device, MEMB_B200_DEVICE,
+                            true, stream);
 }
 
 memb_b200_status memb_b200_union_lookup_words(memb_b200_reader* const* readers, uint32_t num_readers,

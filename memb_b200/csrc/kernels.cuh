@@ -266,8 +266,8 @@ __global__ void measure_rows_kernel(const uint8_t* __restrict__ packed, uint64_t
 __global__ void repack_rows_kernel(const uint8_t* __restrict__ packed, uint64_t packedSize,
                                    const uint32_t* __restrict__ valueOffsets,
                                    const uint32_t* __restrict__ rowBytes,
-                                   const uint32_t* __restrict__ rowOff16, uint32_t rows, uint32_t padBits,
-                                   uint32_t* __restrict__ blob)
+                                   const uint32_t* __restrict__ rowOff16, uint32_t recUnits, uint32_t rows,
+                                   uint32_t padBits, uint32_t* __restrict__ blob)
 {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) / WARP;
     const uint32_t lane = threadIdx.x % WARP;
@@ -276,8 +276,9 @@ __global__ void repack_rows_kernel(const uint8_t* __restrict__ packed, uint64_t 
     }
     const uint64_t src = valueOffsets[warp];
     const uint32_t bytes = rowBytes[warp];
-    const uint32_t words = (rowOff16[warp + 1] - rowOff16[warp]) * TRAINED_UNIT_WORDS;
-    uint32_t* dst = blob + static_cast<uint64_t>(rowOff16[warp]) * TRAINED_UNIT_WORDS;
+    // recUnits != 0: fixed-stride records (TrainedParams::recUnits), else the offset table
+    const uint32_t words = (recUnits ? recUnits : rowOff16[warp + 1] - rowOff16[warp]) * TRAINED_UNIT_WORDS;
+    uint32_t* dst = blob + (recUnits ? static_cast<uint64_t>(warp) * recUnits : static_cast<uint64_t>(rowOff16[warp])) * TRAINED_UNIT_WORDS;
     // big-endian word `wi` of the row as stored in the file (zero outside the row)
     auto fileWord = [&](int64_t wi) -> uint32_t {
         uint32_t v = 0;
@@ -350,8 +351,11 @@ __global__ void pad_rows16_kernel(const uint32_t* __restrict__ rowBytes, uint32_
 // streaming store covering 128 contiguous bytes per 8 lanes.
 struct TrainedParams {
     const RowUnit* blob;
-    const uint32_t* rowOff16;   // (name from the 16 B layout) rows+1 offsets into blob in UNITS
+    const uint32_t* rowOff16;   // (name from the 16 B layout) rows+1 offsets into blob in UNITS; unused when recUnits != 0
+    uint32_t recUnits;          // != 0: fixed-stride records, row r at blob + r * recUnits (no offset table)
     const uint32_t* lut;
+    const uint32_t* lut2;       // second level: entries of codes longer than the LUT is wide (lut2Entries of them)
+    uint32_t lut2Entries;
     const float* codebook;
     const CanonicalCode* code;
     uint32_t rows;
@@ -404,6 +408,7 @@ __host__ __device__ inline uint32_t trainedWarpBytes(uint32_t rowWords)
 // (`base` = address of the first dynamic shared byte, 1 KiB on sm_100).
 struct TrainedLayout {
     uint32_t codebook;   // 1 KiB aligned
+    uint32_t lut2;       // second-level entries, right after the codebooks
     uint32_t lut;        // aligned to lutBytes
     uint32_t lowStart;   // warps [0, lowWarps) at lowStart + w * perWarp
     uint32_t lowWarps;
@@ -411,11 +416,12 @@ struct TrainedLayout {
     uint32_t end;        // first byte not used
 };
 __host__ __device__ inline TrainedLayout trainedLayout(uint32_t base, uint32_t lutBytes, uint32_t perWarp,
-                                                       uint32_t warps)
+                                                       uint32_t warps, uint32_t lut2Entries)
 {
     TrainedLayout l;
     l.codebook = (base + 1023u) & ~1023u;
-    l.lowStart = l.codebook + TRAINED_CODEBOOK_BYTES;
+    l.lut2 = l.codebook + TRAINED_CODEBOOK_BYTES;
+    l.lowStart = (l.lut2 + lut2Entries * 4u + 127u) & ~127u;
     l.lut = (l.lowStart + lutBytes - 1) / lutBytes * lutBytes;
     const uint32_t fit = (l.lut - l.lowStart) / perWarp;
     l.lowWarps = fit < warps ? fit : warps;
@@ -445,19 +451,6 @@ __global__ void smem_base_probe_kernel(uint32_t* out)
 {
     extern __shared__ __align__(128) unsigned char probeSmem[];
     *out = smemAddr(probeSmem);
-}
-
-// Slow path for a window whose code is longer than the LUT width.  `window`
-// holds the next stream bits MSB-first (at least 16 valid).
-__device__ __noinline__ uint32_t escapeDecode(const CanonicalCode* __restrict__ code, uint32_t window, uint32_t symShift)
-{
-    for (uint32_t l = code->minLen; l <= code->maxLen; ++l) {
-        const uint32_t rel = (l ? (window >> (32 - l)) : 0u) - code->firstCode[l];
-        if (rel < code->count[l]) {
-            return ((static_cast<uint32_t>(code->keys[code->firstIndex[l] + rel]) << symShift) << 16) | l;
-        }
-    }
-    return 0;
 }
 
 // ---- shared-memory accessors on 32-bit shared-window addresses ----
@@ -596,6 +589,8 @@ struct LaneDecoder {
     uint32_t lutLane;    // LUT base | lane * 4 (bank-replicated LUT) or LUT base (single copy)
     uint32_t lutMask;
     uint32_t rowLane;    // word w of this lane's compressed row lives at rowLane + w * 128
+    uint32_t lut2;       // second-level table (ESCAPE)
+    uint32_t padL;       // padBits + lutBits: where the bits after the LUT window start
 };
 
 // Re-centre the 64-bit window on the row's current bit position: three loads
@@ -616,7 +611,10 @@ __device__ __forceinline__ uint32_t decodeSymbol(LaneDecoder& d, const TrainedPa
     uint32_t e = ldsU32((d.lo & d.lutMask) | d.lutLane);
     if (ESCAPE) {
         if (e & 0x8000u) {
-            e = escapeDecode(p.code, __brev(d.lo >> p.padBits), p.symShift);
+            // a code longer than the LUT is wide: second-level table indexed by the bits that
+            // follow the window (src/huffman_table_decoder.h:58-93,108-116)
+            const uint32_t idx = (e >> 16) + ((d.lo >> d.padL) & ((1u << (e & 15u)) - 1u));
+            e = ldsU32(d.lut2 + idx * 4u);
         }
     }
     d.lo = __funnelshift_r(d.lo, d.hi, e);  // shift = e & 31 = code length
@@ -752,7 +750,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
 
     const uint32_t lutBytes = trainedLutBytes(p.lutBits, p.lutReplicas);
     const uint32_t base = smemAddr(smem);
-    const TrainedLayout lay = trainedLayout(base, lutBytes, trainedWarpBytes(p.rowWords), warpsPerCta);
+    const TrainedLayout lay = trainedLayout(base, lutBytes, trainedWarpBytes(p.rowWords), warpsPerCta, p.lut2Entries);
     {
         uint32_t dynBytes;
         asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dynBytes));
@@ -791,6 +789,12 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                 }
             }
         }
+        if (ESCAPE) {
+            uint32_t* lut2S = reinterpret_cast<uint32_t*>(smem + (lay.lut2 - base));
+            for (uint32_t i = threadIdx.x; i < p.lut2Entries; i += blockDim.x) {
+                lut2S[i] = p.lut2[i];
+            }
+        }
         for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) {
             cbS[i] = i < p.codebookSize ? p.codebook[i] : 0.f;
             if (SYM == 2) {
@@ -810,6 +814,8 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     d.lutLane = lay.lut | (p.lutReplicas == 1 ? 0u : lane * 4u);
     d.lutMask = p.lutMask;
     d.rowLane = warpBase + lane * 4;
+    d.lut2 = lay.lut2;
+    d.padL = p.padBits + p.lutBits;
     const uint32_t tileLane = tileRowBase(tile, lane);
     // The flush reads ring slots it then does not store (units before the row in the
     // first chunk, units past it in the last).  With SMALLCB a symbol byte IS a shared
@@ -852,8 +858,13 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         lo = hi = 0;
         if (p.rows) {
             const uint32_t r = ok ? row : 0u;
-            lo = __ldg(p.rowOff16 + r);
-            hi = __ldg(p.rowOff16 + r + 1);
+            if (p.recUnits) {
+                lo = r * p.recUnits;
+                hi = lo + p.recUnits;
+            } else {
+                lo = __ldg(p.rowOff16 + r);
+                hi = __ldg(p.rowOff16 + r + 1);
+            }
         }
         return ok;
     };
@@ -1203,9 +1214,10 @@ __global__ void trained_decode_generic_kernel(const TrainedParams p, const int32
     const int64_t row = ids ? static_cast<int64_t>(ids[i]) : static_cast<int64_t>(rowBegin) + static_cast<int64_t>(i);
     const bool present = row >= 0 && row < static_cast<int64_t>(p.rows);
     float* dst = o.out + i * o.rowStride + o.colOffset;
-    const uint32_t* words = present ? reinterpret_cast<const uint32_t*>(p.blob + p.rowOff16[row]) : nullptr;
+    const uint64_t firstUnit = !present ? 0 : p.recUnits ? static_cast<uint64_t>(row) * p.recUnits : p.rowOff16[row];
+    const uint32_t* words = present ? reinterpret_cast<const uint32_t*>(p.blob + firstUnit) : nullptr;
     const uint64_t limitWords =
-        present ? static_cast<uint64_t>(p.rowOff16[row + 1] - p.rowOff16[row]) * TRAINED_UNIT_WORDS : 0;
+        !present ? 0 : static_cast<uint64_t>(p.recUnits ? p.recUnits : p.rowOff16[row + 1] - p.rowOff16[row]) * TRAINED_UNIT_WORDS;
     uint64_t bit = 0;
     for (uint32_t c = 0; c < p.dim; ++c) {
         float v = 0.f;

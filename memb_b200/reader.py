@@ -1,47 +1,82 @@
-"""Reader — mirrors python/memb/reader.py:5-111 of the reference.
+"""Reader — the drop-in for python/memb/reader.py:5-111 of the reference.
 
-Every lookup runs on the GPU through `_memb` (C ABI -> sm_100a kernels).
-Additive API (not in the reference): `device=` constructor keyword,
-`resolve`, `batch_embedding_ids`, `decode_range`, `load_stats`; the keyword
-`as_tensor=True` on every lookup returns a `torch.Tensor` that stays on the
-reader's GPU (the consumer is an embedding layer on that GPU),
-and `words` may also be a NumPy 'S'/'U' array or a `(blob, offsets)` pair of
-UTF-8 bytes and uint64 offsets (no per-word Python objects).
+Every lookup runs on the GPU through `_memb` (C ABI -> sm_100a kernels); there is no
+CPU decode.  Same names, arguments and exceptions as the reference; additive API (not
+in the reference): `device=` constructor keyword, `resolve`, `batch_embedding_ids`,
+`decode_range`, `to_tensor`, `load_stats`; the keyword `as_tensor=True` on every lookup
+returns a `torch.Tensor` that stays on the reader's GPU (the consumer is
+an embedding layer on that GPU), and `words` may also be a NumPy 'S'/'U' array or a
+`(blob, offsets)` pair of UTF-8 bytes and uint64 offsets (no per-word
+Python objects).
 """
 from abc import ABC, abstractmethod
 
 from . import _memb
 
 
+def _cuda(device):
+    import torch
+    return torch.device('cuda', device)
+
+
 def _device_rows(device, rows, dim):
     import torch
-    return torch.empty((rows, dim), dtype=torch.float32, device=torch.device('cuda', device))
+    return torch.empty((rows, dim), dtype=torch.float32, device=_cuda(device))
+
+
+def _current_stream(device):
+    import torch
+    return torch.cuda.current_stream(_cuda(device)).cuda_stream
+
+
+def _gensim_keyed_vectors():
+    try:
+        from gensim.models import KeyedVectors
+    except ImportError:
+        raise ImportError('You must install gensim for KeyedVectors export')
+    return KeyedVectors
+
+
+def tokenizer_word_list(tokenizer):
+    '''Words of a keras Tokenizer as a dense list indexed by token id: what
+    python/memb/reader.py:100-109 hands to batch_embedding.  Ids run from 1, so slot 0 --
+    like every id the tokenizer does not use -- holds '' (looked up like any word: a zero
+    row unless '' is in the vocabulary).  With `num_words` set only ids below it are kept
+    and the list has exactly `num_words` slots.'''
+    vocabulary = tokenizer.word_index
+    limit = tokenizer.num_words
+    if limit is None:
+        size = max(vocabulary.values()) + 1
+        kept = vocabulary.items()
+    else:
+        size = limit
+        kept = [(word, token) for word, token in vocabulary.items() if token < limit]
+    slots = [''] * size
+    for word, token in kept:
+        slots[token] = word
+    return slots
 
 
 class BaseReader(ABC):
+    '''What Reader and ReadersUnion have in common (python/memb/reader.py:5-46).'''
+
     def __getitem__(self, key):
-        '''Vector for a word (1-D) or a list of words (2-D).'''
-        if isinstance(key, str):
-            return self.word_embedding(key)
-        elif isinstance(key, list):
-            return self.batch_embedding(key)
-        else:
-            raise TypeError('Key type is not supported')
+        '''reader[word] -> 1-D vector, reader[[words]] -> 2-D matrix.'''
+        for kind, lookup in ((str, self.word_embedding), (list, self.batch_embedding)):
+            if isinstance(key, kind):
+                return lookup(key)
+        raise TypeError('Key type is not supported')
 
     def to_keyed_vectors(self):
-        '''Export model content to a gensim KeyedVectors object.'''
-        try:
-            from gensim.models import KeyedVectors
-        except ImportError:
-            raise ImportError('You must install gensim for KeyedVectors export')
-
-        keyed_vectors = KeyedVectors(self.dim)
-        words = self.keys()
-        keyed_vectors.add(words, self._all_rows(words))
+        '''The whole model as a gensim KeyedVectors object (python/memb/reader.py:19-30).'''
+        keyed_vectors = _gensim_keyed_vectors()(self.dim)
+        vocabulary = self.keys()
+        keyed_vectors.add(vocabulary, self._all_rows(vocabulary))
         return keyed_vectors
 
-    def _all_rows(self, words):
-        return self.batch_embedding(words)
+    def _all_rows(self, vocabulary):
+        # one row per entry of keys(), in that order
+        return self.batch_embedding(vocabulary)
 
     @abstractmethod
     def keys(self):
@@ -58,22 +93,6 @@ class BaseReader(ABC):
     @abstractmethod
     def tokenizer_embedding(self, tokenizer):
         pass
-
-
-def tokenizer_word_list(tokenizer):
-    '''Dense word list indexed by keras token id (python/memb/reader.py:100-109):
-    index 0 and every gap hold '' (which is looked up like any other word).'''
-    word_indices = tokenizer.word_index.items()
-    if tokenizer.num_words is not None:
-        word_indices = [item for item in word_indices if item[1] < tokenizer.num_words]
-        max_index = tokenizer.num_words
-    else:
-        max_index = max([item[1] for item in word_indices]) + 1
-
-    sorted_word_list = [''] * max_index
-    for word, idx in word_indices:
-        sorted_word_list[idx] = word
-    return sorted_word_list
 
 
 class Reader(BaseReader):
@@ -116,16 +135,20 @@ class Reader(BaseReader):
         '''2-D float32 array for a list of words; absent words give zero rows.'''
         if not as_tensor:
             return self._impl.batch_embedding(words)
-        out = _device_rows(self._impl.device(), _memb.Reader.count_words(words), self.dim)
-        self._impl.batch_embedding_into(words, out.data_ptr(), out.shape[0], True)
+        # marshal once; resolve + decode are queued on torch's CURRENT stream, so they are
+        # ordered after whatever still uses the block the caching allocator hands out
+        packed = words if isinstance(words, tuple) else _memb.pack_words(words)
+        device = self._impl.device()
+        out = _device_rows(device, len(packed[1]) - 1, self.dim)
+        self._impl.batch_embedding_into(packed, out.data_ptr(), out.shape[0], True, _current_stream(device))
         return out
 
     def tokenizer_embedding(self, tokenizer, as_tensor=False):
         '''Weights of an Embedding layer for a keras Tokenizer.'''
         return self.batch_embedding(tokenizer_word_list(tokenizer), as_tensor=as_tensor)
 
-    def _all_rows(self, words):
-        # full-vocabulary decode needs no word resolution: rows 0..V-1
+    def _all_rows(self, vocabulary):
+        # keys() is the row-id order: the full-vocabulary decode needs no word resolution
         return self._impl.decode_range(0, self._impl.rows())
 
     # ---- additive ----
@@ -144,12 +167,11 @@ class Reader(BaseReader):
         if not as_tensor:
             return self._impl.batch_embedding_ids(ids)
         import torch
-        device = torch.device('cuda', self._impl.device())
+        device = _cuda(self._impl.device())
         ids = torch.as_tensor(ids, dtype=torch.int32).to(device).contiguous().reshape(-1)
         out = _device_rows(self._impl.device(), ids.numel(), self.dim)
-        with torch.cuda.device(device):
-            stream = torch.cuda.current_stream().cuda_stream
-            self._impl.decode_ids_into(ids.data_ptr(), True, ids.numel(), out.data_ptr(), True, stream)
+        self._impl.decode_ids_into(ids.data_ptr(), True, ids.numel(), out.data_ptr(), True,
+                                   _current_stream(self._impl.device()))
         ids.record_stream(torch.cuda.current_stream(device))
         return out
 
@@ -157,12 +179,10 @@ class Reader(BaseReader):
         '''Rows [begin, end) in row-id order as a (end-begin, dim) float32 array.'''
         if not as_tensor:
             return self._impl.decode_range(begin, end)
-        import torch
         if not 0 <= begin <= end <= self._impl.rows():
             raise ValueError('decode_range: rows out of range')
         out = _device_rows(self._impl.device(), end - begin, self.dim)
-        with torch.cuda.device(out.device):
-            self._impl.decode_range_into(begin, end, out.data_ptr(), True, torch.cuda.current_stream().cuda_stream)
+        self._impl.decode_range_into(begin, end, out.data_ptr(), True, _current_stream(self._impl.device()))
         return out
 
     def to_tensor(self):

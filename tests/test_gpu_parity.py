@@ -141,6 +141,37 @@ def test_trained_edge_codes(abi, oracle, workdir):
             reader.close()
 
 
+@pytest.mark.parametrize("bits", [1, 4, 6, 8])
+def test_trained_kernel_variants(abi, oracle, synthetic, bits):
+    """The same table through every trained path: whole-row kernel on fixed-stride records
+    (default), ring kernel on records, ring kernel on the offset table; single lookups and a
+    union of the table with a second one; ids with misses, ragged tiles."""
+    syn, other = synthetic("trained", bits, rows=3000, dim=300), synthetic("trained", 5, rows=2500, dim=300, seed=77)
+    want, want_other = oracle.open(syn.path), oracle.open(other.path)
+    rng = np.random.default_rng(100 + bits)
+    ids = rng.integers(-3, 3003, 4100).astype(np.int32)
+    ids2 = np.stack([ids, rng.integers(-3, 2503, 4100).astype(np.int32)])
+    parts = [want.batch_ids(ids2[0]), want_other.batch_ids(ids2[1])]
+    try:
+        for rows_kernel, fixed in ((2, 1), (1, 1), (0, 1), (0, 0), (2, 0)):
+            abi.check(abi.lib.memb_b200_set_option(b"trained_rows_kernel", rows_kernel))
+            abi.check(abi.lib.memb_b200_set_option(b"trained_fixed_records", fixed))
+            reader, second = abi.open_checked(syn.path), abi.open_checked(other.path)
+            tag = (bits, rows_kernel, fixed)
+            assert bits_equal(reader.decode_range(0, 3000), want.decode_range(0, 3000)), tag
+            assert bits_equal(reader.decode_range(17, 1030), want.decode_range(17, 1030)), tag
+            assert bits_equal(reader.decode_ids(ids), parts[0]), tag
+            assert bits_equal(helpers.union_decode_ids(abi, [reader, second], abi.AVERAGE, ids2, 300),
+                              np.mean(parts, axis=0)), tag
+            assert bits_equal(helpers.union_decode_ids(abi, [reader, second], abi.CONCATENATE, ids2, 600),
+                              np.concatenate(parts, axis=-1)), tag
+            reader.close()
+            second.close()
+    finally:
+        abi.lib.memb_b200_set_option(b"trained_rows_kernel", 1)
+        abi.lib.memb_b200_set_option(b"trained_fixed_records", 1)
+
+
 def test_lut_layouts_do_not_change_results(abi, oracle, synthetic):
     """GPU analogue of trainedBuilderWorksWithIndirectDecoder (tests.cpp:76-88):
     every LUT layout / kernel variant decodes the same bits."""
@@ -584,9 +615,14 @@ def test_union_average_through_symbol_words(abi, oracle, synthetic, bits0, bits1
     parts = [o.batch_embedding(words) for o in oracles]
     for count in (2, 3):
         want = np.mean(parts[:count], axis=0)
+        # default: two trained readers = ONE launch of trained_rows_kernel
         assert bits_equal(helpers.union_lookup_words(abi, readers[:count], abi.AVERAGE, words, dim), want)
         try:
+            # the multi-launch ring path: symbol words, then plain read-modify-write
+            abi.check(abi.lib.memb_b200_set_option(b"trained_rows_kernel", 0))
+            assert bits_equal(helpers.union_lookup_words(abi, readers[:count], abi.AVERAGE, words, dim), want)
             abi.check(abi.lib.memb_b200_set_option(b"union_symbol_average", 0))
             assert bits_equal(helpers.union_lookup_words(abi, readers[:count], abi.AVERAGE, words, dim), want)
         finally:
             abi.lib.memb_b200_set_option(b"union_symbol_average", 1)
+            abi.lib.memb_b200_set_option(b"trained_rows_kernel", 1)
