@@ -94,6 +94,13 @@ memb_b200_status memb_b200_keys(const memb_b200_reader* reader, const char** wor
  * ids_host[i] = row id or -1.  Runs on the device (vocabulary hash). */
 memb_b200_status memb_b200_resolve(memb_b200_reader* reader, const char* query_bytes,
                                    const uint64_t* query_offsets, uint64_t n, int32_t* ids_host);
+/* The same with every buffer already on the reader's device (additive): query text, n+1
+ * offsets and the n ids are DEVICE pointers; the resolve kernel is queued on `stream` and
+ * the call returns without waiting (feeds memb_b200_decode_ids / union_decode_ids with
+ * device ids; lets a caller time K0 alone). */
+memb_b200_status memb_b200_resolve_device(memb_b200_reader* reader, const char* query_bytes_device,
+                                          const uint64_t* query_offsets_device, uint64_t n,
+                                          int32_t* ids_device, void* stream);
 
 /* Reader::batchEmbeddingToBuffer(words, buffer) — src/reader.cpp:59-86.
  * out_host: n*dim floats, row-major. */

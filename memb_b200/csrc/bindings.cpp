@@ -494,6 +494,14 @@ public:
         return ids;
     }
 
+    // raw-pointer form: query blob, offsets and ids already on the device; asynchronous on `stream`
+    void resolveInto(uintptr_t queryBytes, uintptr_t queryOffsets, uint64_t n, uintptr_t ids, uintptr_t stream) const
+    {
+        check(memb_b200_resolve_device(impl_, reinterpret_cast<const char*>(queryBytes),
+                                       reinterpret_cast<const uint64_t*>(queryOffsets), n,
+                                       reinterpret_cast<int32_t*>(ids), reinterpret_cast<void*>(stream)));
+    }
+
     py::array_t<float> batchEmbeddingIds(py::array_t<int32_t, py::array::c_style | py::array::forcecast> ids) const
     {
         const size_t n = static_cast<size_t>(ids.size());
@@ -723,6 +731,8 @@ PYBIND11_MODULE(_memb, m)
         .def("rows", &Reader::rows)
         .def("device", &Reader::device)
         .def("resolve", &Reader::resolve)
+        .def("resolve_into", &Reader::resolveInto, py::arg("query_bytes"), py::arg("query_offsets"), py::arg("n"),
+             py::arg("ids"), py::arg("stream") = 0)
         .def("batch_embedding_ids", &Reader::batchEmbeddingIds)
         .def("batch_embedding_into", &Reader::batchEmbeddingInto, py::arg("words"), py::arg("out"),
              py::arg("capacity_rows"), py::arg("out_on_device"), py::arg("stream") = 0)

@@ -1490,6 +1490,19 @@ memb_b200_status memb_b200_resolve(memb_b200_reader* reader, const char* query_b
     });
 }
 
+memb_b200_status memb_b200_resolve_device(memb_b200_reader* reader, const char* query_bytes_device,
+                                          const uint64_t* query_offsets_device, uint64_t n, int32_t* ids_device,
+                                          void* stream)
+{
+    return guarded([&] {
+        if (!reader || (n && (!query_bytes_device || !query_offsets_device || !ids_device))) {
+            fail(MEMB_B200_ERR_ARGUMENT, "resolve_device: null argument");
+        }
+        DeviceGuard guard(reader->device);
+        launchResolve(*reader, query_bytes_device, query_offsets_device, n, ids_device, static_cast<cudaStream_t>(stream));
+    });
+}
+
 static memb_b200_status lookupWords(memb_b200_reader* reader, const char* query_bytes, const uint64_t* query_offsets,
                                     uint64_t n, float* out, memb_b200_mem_kind out_kind, bool callerStream,
                                     void* stream)

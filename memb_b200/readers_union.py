@@ -1,51 +1,25 @@
-"""ReadersUnion — mirrors python/memb/readers_union.py:5-104 of the reference.
+"""ReadersUnion — the drop-in for python/memb/readers_union.py:5-104 of the reference.
 
-The merge (np.mean(axis=0) / np.concatenate(axis=-1) in the reference) is fused
-into the GPU decode: no per-reader (n, dim) temporaries exist.
+The reference merges per-reader (n, dim) NumPy batches with np.mean(axis=0) or
+np.concatenate(axis=-1) (:16-18, :30-32).  Here a union of Readers is ONE native call:
+every reader's words are resolved on the GPU and the merge is fused into the decode
+(trained readers: one kernel launch, memb_b200/csrc/trained_rows.cuh), so no per-reader
+batch ever exists.  A union with a nested memb_b200 union among its members merges the
+members' device tensors on the GPU with the same arithmetic -- fp32 adds in member order,
+then one fp32 divide by the member count.  The reference accepts ANY object with the reader
+interface; such foreign members hand back host arrays of their own, and only those are
+merged on the host (the one host-side merge in the package: nothing of memb_b200's own
+lookup path runs there).
 """
 import numpy as np
 
 from . import _memb
 from .reader import BaseReader, Reader, tokenizer_word_list
 
-
-class AverageUnionMaker:
-    name = 'average'
-
-    @staticmethod
-    def check(readers):
-        dims = [reader.dim for reader in readers]
-        if any(dim != dims[0] for dim in dims):
-            raise AssertionError('Dimensions of all readers must be equal for average mode')
-
-    @staticmethod
-    def dim(reader_dims):
-        return reader_dims[0]
-
-    @staticmethod
-    def merge(vectors):
-        return np.mean(vectors, axis=0)
-
-
-class ConcatenatedUnionMaker:
-    name = 'concatenate'
-
-    @staticmethod
-    def check(readers):
-        pass
-
-    @staticmethod
-    def dim(reader_dims):
-        return sum(reader_dims)
-
-    @staticmethod
-    def merge(vectors):
-        return np.concatenate(vectors, axis=-1)
-
-
-UNION_MAKERS = {
-    'average': AverageUnionMaker(),
-    'concatenate': ConcatenatedUnionMaker(),
+# mode -> (dimension of the merged vectors, whether every member must have the same dim)
+_MODES = {
+    'average': (lambda dims: dims[0], True),
+    'concatenate': (sum, False),
 }
 
 
@@ -58,62 +32,80 @@ class ReadersUnion(BaseReader):
     readers : list of Reader
     mode : str
         'average' or 'concatenate'
+
+    Attributes
+    ----------
+    dim : int
+        Dimension of vectors after merge
     '''
 
     def __init__(self, readers, mode):
         super().__init__()
-
+        # same checks, order and messages as python/memb/readers_union.py:56-69
         if len(readers) < 2:
             raise AssertionError('You must pass at least 2 readers to create a union')
-
-        self._union_maker = UNION_MAKERS.get(mode)
-        if self._union_maker is None:
-            raise KeyError('Mode {} is not supported. Available modes are {}'.format(
-                mode, list(UNION_MAKERS.keys())))
-
-        self._union_maker.check(readers)
+        if mode not in _MODES:
+            raise KeyError('Mode {} is not supported. Available modes are {}'.format(mode, list(_MODES.keys())))
+        merged_dim, equal_dims = _MODES[mode]
+        if equal_dims and len({reader.dim for reader in readers}) > 1:
+            raise AssertionError('Dimensions of all readers must be equal for average mode')
+        self._mode = mode
+        self._merged_dim = merged_dim
         self._readers = readers
-        # the fused kernel path needs native readers; anything else (e.g. a
-        # nested union) is merged with the reference's NumPy expressions
         self._native = all(isinstance(reader, Reader) for reader in readers)
+        self._on_device = all(isinstance(reader, (Reader, ReadersUnion)) for reader in readers)
 
     @property
     def dim(self):
-        return self._union_maker.dim([reader.dim for reader in self._readers])
+        return self._merged_dim([reader.dim for reader in self._readers])
 
     def keys(self):
         '''Union of keys contained in wrapped models'''
-        all_keys = set()
-        for reader in self._readers:
-            all_keys |= set(reader.keys())
-
-        return sorted(all_keys)
+        return sorted(set().union(*(reader.keys() for reader in self._readers)))
 
     def word_embedding(self, word, as_tensor=False):
         '''Merged vectors from all readers for a single word'''
-        if self._native:
-            return self.batch_embedding([word], as_tensor=as_tensor)[0]
-        return self._union_maker.merge([reader.word_embedding(word) for reader in self._readers])
+        return self.batch_embedding([word], as_tensor=as_tensor)[0]
 
     def batch_embedding(self, words, as_tensor=False):
         '''Merged vectors from all readers for a list of words.
-        as_tensor=True (additive, native readers only): CUDA tensor on the readers' GPU.'''
-        if self._native:
-            impls = [reader._impl for reader in self._readers]
+        as_tensor=True (additive): CUDA tensor on the readers' GPU.'''
+        if not self._on_device:
             if as_tensor:
-                import torch
-                device = torch.device('cuda', impls[0].device())
-                out = torch.empty((_memb.Reader.count_words(words), self.dim), dtype=torch.float32, device=device)
-                _memb.union_batch_embedding_into(impls, self._union_maker.name, words, out.data_ptr(),
-                                                 out.shape[0], True)
-                return out
-            return _memb.union_batch_embedding(impls, self._union_maker.name, words)
-        if as_tensor:
-            raise TypeError('as_tensor needs native Readers in the union')
-        return self._union_maker.merge([reader.batch_embedding(words) for reader in self._readers])
+                raise TypeError('as_tensor needs memb_b200 Readers or ReadersUnions in the union')
+            return self._merge_foreign([reader.batch_embedding(words) for reader in self._readers])
+        if not self._native:
+            merged = self._merge_on_device(words)
+            return merged if as_tensor else merged.cpu().numpy()
+        impls = [reader._impl for reader in self._readers]
+        if not as_tensor:
+            return _memb.union_batch_embedding(impls, self._mode, words)
+        import torch
+        device = torch.device('cuda', impls[0].device())
+        packed = words if isinstance(words, tuple) else _memb.pack_words(words)
+        out = torch.empty((len(packed[1]) - 1, self.dim), dtype=torch.float32, device=device)
+        _memb.union_batch_embedding_into(impls, self._mode, packed, out.data_ptr(), out.shape[0], True,
+                                         torch.cuda.current_stream(device).cuda_stream)
+        return out
 
     def tokenizer_embedding(self, tokenizer, as_tensor=False):
         '''Merged results of tokenizer_embedding from all readers'''
-        if self._native:
-            return self.batch_embedding(tokenizer_word_list(tokenizer), as_tensor=as_tensor)
-        return self._union_maker.merge([reader.tokenizer_embedding(tokenizer) for reader in self._readers])
+        return self.batch_embedding(tokenizer_word_list(tokenizer), as_tensor=as_tensor)
+
+    def _merge_on_device(self, words):
+        # members that are unions themselves: each yields a device tensor, merged here with
+        # torch ops on the GPU in the reference's order (sequential fp32 adds, one true divide)
+        import torch
+        parts = [reader.batch_embedding(words, as_tensor=True) for reader in self._readers]
+        if self._mode == 'concatenate':
+            return torch.cat(parts, dim=-1)
+        total = parts[0].clone()
+        for part in parts[1:]:
+            total += part
+        total /= float(len(parts))
+        return total
+
+    def _merge_foreign(self, arrays):
+        # host arrays produced by reader objects that are not memb_b200's
+        # (python/memb/readers_union.py:16-18,30-32)
+        return np.concatenate(arrays, axis=-1) if self._mode == 'concatenate' else np.mean(arrays, axis=0)

@@ -128,6 +128,74 @@ def pack_row(symbols, code_of, len_of):
     return np.packbits(np.array(bits, np.uint8)).tobytes()
 
 
+def pack_rows_numpy(symbols, keys, lengths, chunk_rows=10000, threads=None):
+    """Vectorised pack_row for a (rows, dim) uint8 symbol matrix: returns (packed bytes of all rows
+    back to back, each zero padded to a byte; uint64 byte offset of every row).  Chunks of rows
+    are packed on a thread pool (NumPy releases the GIL in the heavy calls)."""
+    import os
+    from concurrent.futures import ThreadPoolExecutor
+
+    symbols = np.ascontiguousarray(symbols, np.uint8)
+    codes = canonical_codes([int(v) for v in lengths])
+    aligned = np.zeros(256, ">u2")  # code left-aligned in 16 bits, big-endian: unpackbits yields it MSB-first
+    len_of = np.zeros(256, np.uint8)
+    for k, c, n in zip(keys, codes, lengths):
+        aligned[int(k)], len_of[int(k)] = (c << (16 - int(n))) & 0xffff, n
+    rows, dim = symbols.shape
+    bit_index = np.arange(16, dtype=np.uint8)[None, None, :]
+    starts = list(range(0, rows, chunk_rows))
+
+    def pack(begin):
+        sym = symbols[begin:begin + chunk_rows]
+        lens = len_of[sym]
+        bits = np.unpackbits(aligned[sym].view(np.uint8).reshape(len(sym), dim, 2), axis=-1)  # (r, dim, 16)
+        valid = bit_index < lens[:, :, None]
+        total = lens.sum(axis=1, dtype=np.int64)
+        pad = (-total) % 8
+        pad_valid = np.arange(8)[None, :] < pad[:, None]     # zero bits up to the byte boundary
+        flat_valid = np.concatenate([valid.reshape(len(sym), -1), pad_valid], axis=1)
+        flat_bits = np.concatenate([bits.reshape(len(sym), -1), np.zeros((len(sym), 8), np.uint8)], axis=1)
+        return np.packbits(flat_bits[flat_valid]), (total + pad) // 8
+
+    with ThreadPoolExecutor(threads or min(32, os.cpu_count() or 1)) as pool:
+        done = list(pool.map(pack, starts))
+    row_bytes = np.concatenate([d[1] for d in done]).astype(np.uint64) if done else np.zeros(0, np.uint64)
+    offsets = np.zeros(rows, np.uint64)
+    np.cumsum(row_bytes[:-1], out=offsets[1:])
+    return np.concatenate([d[0] for d in done]) if done else np.zeros(0, np.uint8), offsets
+
+
+def write_trained_packed(path, sorted_words, packed, value_offsets, keys, lengths, centroids, dim):
+    """Trained file from rows that are already packed: sorted_words in row-id order (bytes, sorted),
+    value_offsets[i] = byte offset of row i in `packed`."""
+    lengths = [int(v) for v in lengths]
+    blob = b"\0".join(sorted_words) + (b"\0" if sorted_words else b"")
+    sizes = np.fromiter((len(w) + 1 for w in sorted_words), np.uint64, len(sorted_words))
+    wo = np.zeros(len(sorted_words), np.uint32)
+    if len(sorted_words):
+        wo[1:] = np.cumsum(sizes[:-1])
+    vo = np.asarray(value_offsets).astype(np.uint32)
+    so = np.array(size_offsets_from_lengths(lengths), np.uint32)
+    packed = np.ascontiguousarray(packed, np.uint8)
+
+    def storage(w):
+        def decoder():
+            return w.table([(0, "O", lambda: w.vector(np.array([int(k) for k in keys], np.uint8), 1)),
+                            (1, "O", lambda: w.vector(so))])
+
+        def clusterizer():
+            return w.table([(0, "O", lambda: w.vector(np.asarray(centroids, np.float32)))])
+
+        return lambda: w.table([
+            (0, "O", lambda: w.vector(wo)), (1, "O", lambda: w.vector(vo)),
+            (2, "O", lambda: w.string(blob)), (3, "O", lambda: w.vector(packed, 1)),
+            (4, "O", decoder), (5, "O", clusterizer)])
+
+    data = _finish(3, dim, storage)
+    with open(path, "wb") as f:
+        f.write(data)
+
+
 def write_trained(path, words, symbol_rows, keys, lengths, centroids, dim=None, row_order=None, tail=b""):
     """words: list of bytes in ANY order (they are sorted here like the compressor does,
     src/trained_compression.cpp:73-79); symbol_rows[i] = the dim symbols (key values)
