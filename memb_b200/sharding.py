@@ -44,9 +44,10 @@ def _rank_world(group=None):
 def all_gather_rows(local, n_total, group=None):
     """Assemble the (n_total, dim) matrix from the per-rank slices of `shard_range`.
 
-    `local` is this rank's (end - begin, dim) tensor.  Slices are padded to the
-    common chunk size ceil(n / G) so that ONE all_gather_into_tensor moves
-    everything; the pad rows are cut off again.  Returns a tensor on local.device."""
+    `local` is this rank's (end - begin, dim) tensor.  The gathered buffer holds `world`
+    slots of ceil(n / G) rows; the local slice is copied into its slot and ONE in-place
+    all_gather_into_tensor moves everything (pad rows of short tail slices are cut off
+    again).  Use `decode_range_gathered` to decode straight into the slot instead."""
     import torch
     import torch.distributed as dist
 
@@ -54,18 +55,48 @@ def all_gather_rows(local, n_total, group=None):
     if world == 1:
         return local
     job = (n_total + world - 1) // world
-    dim = local.shape[1]
     begin, end = shard_range(n_total, rank, world)
     if local.shape[0] != end - begin:
         raise ValueError("local slice has %d rows, rank %d owns %d" % (local.shape[0], rank, end - begin))
-    gathered = torch.empty((world * job, dim), dtype=local.dtype, device=local.device)
-    if local.shape[0] == job:
-        send = local.contiguous()
-    else:
-        send = gathered.new_zeros((job, dim))
-        send[: local.shape[0]] = local
-    dist.all_gather_into_tensor(gathered, send, group=group)
+    gathered = torch.empty((world * job, local.shape[1]), dtype=local.dtype, device=local.device)
+    slot = gathered[rank * job:(rank + 1) * job]
+    slot[: local.shape[0]].copy_(local)
+    dist.all_gather_into_tensor(gathered, slot, group=group)
     return gathered[:n_total]
+
+
+def decode_range_gathered(reader, begin=0, end=None, *, group=None, out=None):
+    """Full-vocabulary decode where EVERY rank ends up with the dense (end - begin, dim) matrix:
+    this rank decodes its row range directly into its slot of the gathered buffer (no send
+    copy, no padded temporary), then one in-place NCCL all-gather.  `out`: optional
+    (world * ceil(n / world), dim) float32 buffer on the reader's device to reuse.
+    Returns the (end - begin, dim) view of it."""
+    import torch
+    import torch.distributed as dist
+
+    rank, world = _rank_world(group)
+    end = reader.rows if end is None else end
+    n = end - begin
+    job = (n + world - 1) // world
+    device = torch.device("cuda", reader._impl.device())
+    if out is None:
+        out = torch.empty((world * job, reader.dim), dtype=torch.float32, device=device)
+    _check_out(out, world * job, reader.dim, device)
+    lo, hi = shard_range(n, rank, world)
+    slot = out[rank * job:(rank + 1) * job]
+    stream = torch.cuda.current_stream(device).cuda_stream
+    reader._impl.decode_range_into(begin + lo, begin + hi, slot.data_ptr(), True, stream)
+    if world > 1:
+        dist.all_gather_into_tensor(out, slot, group=group)
+    return out[:n]
+
+
+def _check_out(out, rows, dim, device):
+    import torch
+
+    if (tuple(out.shape) != (rows, dim) or out.dtype != torch.float32 or not out.is_contiguous()
+            or out.device != device):
+        raise ValueError("out must be a contiguous float32 (%d, %d) tensor on %s" % (rows, dim, device))
 
 
 def decode_range_sharded(reader, begin=0, end=None, *, gather=False, group=None, out=None):
@@ -84,6 +115,7 @@ def decode_range_sharded(reader, begin=0, end=None, *, gather=False, group=None,
     device = torch.device("cuda", reader._impl.device())
     if out is None:
         out = torch.empty((hi - lo, reader.dim), dtype=torch.float32, device=device)
+    _check_out(out, hi - lo, reader.dim, device)
     stream = torch.cuda.current_stream(device).cuda_stream
     reader._impl.decode_range_into(begin + lo, begin + hi, out.data_ptr(), True, stream)
     if gather:

@@ -422,6 +422,87 @@ def test_python_api(oracle, synthetic):
     assert memb_b200._memb.launch_count() > 0
 
 
+def test_to_keyed_vectors_and_nested_unions(oracle, synthetic, monkeypatch):
+    """to_keyed_vectors (python/memb/reader.py:19-30) with a stub of gensim's KeyedVectors: the
+    vectors handed over are the rows of keys(), in that order (a Reader takes them from one
+    decode_range(0, V), a union from one batch over its keys).  A union nested in a union merges
+    on the GPU with np.mean's arithmetic; a foreign reader object still works (host merge)."""
+    import sys
+    import types
+    from memb_b200 import Reader, ReadersUnion
+
+    class KeyedVectors:
+        def __init__(self, vector_size):
+            self.vector_size, self.words, self.vectors = vector_size, None, None
+
+        def add(self, words, vectors):
+            self.words, self.vectors = list(words), np.asarray(vectors)
+
+    gensim, models = types.ModuleType("gensim"), types.ModuleType("gensim.models")
+    models.KeyedVectors = KeyedVectors
+    gensim.models = models
+    monkeypatch.setitem(sys.modules, "gensim", gensim)
+    monkeypatch.setitem(sys.modules, "gensim.models", models)
+
+    a, b, c = (synthetic("trained", 4, rows=3000, dim=300, seed=21), synthetic("trained", 6, rows=2500, dim=300, seed=22),
+               synthetic("uniform", 8, rows=1500, dim=300, seed=23))
+    oa, ob, oc = oracle.open(a.path), oracle.open(b.path), oracle.open(c.path)
+    ra, rb, rc = Reader(a.path), Reader(b.path), Reader(c.path)
+    kv = ra.to_keyed_vectors()
+    assert kv.vector_size == 300 and kv.words == [k.decode() for k in oa.keys()]
+    assert bits_equal(kv.vectors, oa.decode_range(0, 3000))
+    union = ReadersUnion([ra, rb], "average")
+    kv = union.to_keyed_vectors()
+    assert kv.words == sorted(set(a.words) | set(b.words))
+    assert bits_equal(kv.vectors, np.mean([oa.batch_embedding(kv.words), ob.batch_embedding(kv.words)], axis=0))
+
+    rng = np.random.default_rng(12)
+    words = queries_for(a, rng, 400) + queries_for(c, rng, 300)
+    inner = np.mean([oa.batch_embedding(words), ob.batch_embedding(words)], axis=0)
+    nested = ReadersUnion([union, rc], "average")
+    assert bits_equal(nested[words], np.mean([inner, oc.batch_embedding(words)], axis=0))
+    assert bits_equal(nested.batch_embedding(words, as_tensor=True).cpu().numpy(), nested[words])
+    nested_cat = ReadersUnion([rc, union], "concatenate")
+    assert nested_cat.dim == 600 and bits_equal(nested_cat[words], np.concatenate([oc.batch_embedding(words), inner], axis=-1))
+
+    class Foreign:  # any object with the reader interface (python/memb/readers_union.py:90-96 duck-types)
+        dim = 300
+
+        def keys(self):
+            return ["x"]
+
+        def batch_embedding(self, words):
+            return np.full((len(words), 300), 2.0, np.float32)
+
+    mixed = ReadersUnion([ra, Foreign()], "average")
+    assert bits_equal(mixed[words], np.mean([oa.batch_embedding(words), np.full((len(words), 300), 2.0, np.float32)], axis=0))
+
+
+def test_device_results_are_ordered_on_the_callers_stream(oracle, synthetic):
+    """as_tensor=True allocates from torch's caching allocator, which hands out a block as soon as
+    the tensor that owned it is freed -- kernels queued earlier on the stream may still write it.
+    The lookup must therefore be queued on the caller's stream (memb_b200_lookup_words_on)."""
+    import torch
+    from memb_b200 import Reader, ReadersUnion
+
+    syn = synthetic("trained", 4, rows=3000, dim=300, seed=21)
+    other = synthetic("trained", 6, rows=2500, dim=300, seed=22)
+    reader, reader2 = Reader(syn.path), Reader(other.path)
+    rng = np.random.default_rng(3)
+    words = queries_for(syn, rng, 60000)
+    want = oracle.open(syn.path).batch_embedding(words)
+    want_avg = np.mean([want, oracle.open(other.path).batch_embedding(words)], axis=0)
+    union = ReadersUnion([reader, reader2], "average")
+    for lookup, expect in ((reader.batch_embedding, want), (union.batch_embedding, want_avg)):
+        for _ in range(3):
+            scratch = torch.zeros((len(words), 300), dtype=torch.float32, device="cuda")
+            for _ in range(400):  # tens of milliseconds of kernels that write `scratch`
+                scratch.add_(1.0)
+            del scratch  # the block is free for the allocator, the kernels are still queued
+            got = lookup(words, as_tensor=True)
+            assert bits_equal(got.cpu().numpy(), expect)
+
+
 # ---- additive word-collection forms and device-resident results (SURVEY 8(f)-2/3) ----
 def test_word_collection_forms_and_device_tensors(oracle, synthetic):
     import torch
