@@ -226,6 +226,15 @@ void parseTrained(const View& v, size_t t, MembFile& f, unsigned threads)
         std::memcpy(f.code.sizeOffsets.data(), v.data() + sizeOffsets.pos, 4 * sizeOffsets.len);
     }
     buildPrefixCodeTable(f.code);
+    // The load decodes every row once (dim symbols each) to measure it: bound that work by what
+    // the file can hold.  A row of dim codes of at least minLen bits each that starts inside
+    // packed_values cannot be longer than the vector plus the zero bits the reference reads
+    // past its end (src/bit_stream_reader.h:22-25) -- allow 64 KiB of those; a one-symbol code
+    // (zero-bit rows) is bounded by a plain cap.
+    const uint64_t rowBits = static_cast<uint64_t>(f.dim) * std::max(1u, f.code.minLen);
+    if (f.dim > (1u << 24) || rowBits > 8 * (static_cast<uint64_t>(f.packedSize) + 65536)) {
+        throw FormatError("memb file: dim is larger than packed_values can hold rows for");
+    }
 
     const auto centroids = v.vector(clusterizer, I::KMEANS_CENTROIDS, 4);
     if (!centroids.present || centroids.len == 0) {
@@ -255,6 +264,11 @@ void parseNodeStorage(const View& v, size_t t, MembFile& f, unsigned threads)
     }
     f.rows = nodes.len;
     const uint64_t dim = f.dim;
+    // every value of every row lives in the mapping: a header that promises more than the file
+    // holds is corrupt (and would otherwise drive a terabyte-sized allocation below)
+    if (dim != 0 && f.rows > v.size() / (dim * (UNIFORM ? 1 : 4))) {
+        throw FormatError("memb file: rows x dim exceeds the file size");
+    }
     std::vector<View::Span> wordSpans(f.rows), valueSpans(f.rows);
     if (UNIFORM) {
         f.quantizationLevels = v.scalar<uint8_t>(t, I::UNIFORM_LEVELS, 0);

@@ -282,3 +282,171 @@ def write_full(path, words, matrix):
     with open(path, "wb") as f:
         f.write(data)
     return [words[i] for i in by_word]
+
+
+# ---- the layout a real FlatBufferBuilder emits (flatc 1.9.0, what memb_converter produces) ----
+class _BackWriter:
+    """Back-to-front FlatBuffers construction like flatbuffers::FlatBufferBuilder: the buffer
+    grows towards lower addresses, children are finished before their parents (so they sit at
+    HIGHER addresses), fields are added in the order given (the generated Create* helpers add
+    them by descending size), scalars equal to their default are dropped, and identical
+    vtables are shared -- every table after the first with the same shape reaches its vtable
+    through a NEGATIVE soffset.  Offsets handed around are distances from the END of the
+    buffer, as in the C++ builder."""
+
+    def __init__(self):
+        self.buf = bytearray()
+        self.vtables = []  # (bytes, offset from end)
+        self.minalign = 1
+
+    def size(self):
+        return len(self.buf)
+
+    def _push(self, data):
+        self.buf[0:0] = data
+
+    def prealign(self, length, alignment):
+        self.minalign = max(self.minalign, alignment)
+        while (self.size() + length) % alignment:
+            self._push(b"\0")
+
+    def _refer_to(self, off):
+        self.prealign(0, 4)
+        return self.size() - off + 4
+
+    def vector(self, array, elem_size):
+        data = np.ascontiguousarray(array).tobytes()
+        self.prealign(len(data), 4)
+        self.prealign(len(data), elem_size)
+        self._push(data)
+        self._push(struct.pack("<I", len(data) // elem_size))
+        return self.size()
+
+    def string(self, data):
+        self.prealign(len(data) + 1, 4)
+        self._push(bytes(data) + b"\0")
+        self._push(struct.pack("<I", len(data)))
+        return self.size()
+
+    def offset_vector(self, offsets):
+        self.prealign(4 * len(offsets), 4)
+        for off in reversed(offsets):
+            self._push(struct.pack("<I", self._refer_to(off)))
+        self._push(struct.pack("<I", len(offsets)))
+        return self.size()
+
+    def table(self, fields):
+        """fields: (id, fmt, value) in the order a generated Create* adds them; fmt 'O': value is an
+        offset from the end (0 = absent); scalars: None = equal to the default, omitted."""
+        start = self.size()
+        placed = {}
+        for fid, fmt, value in fields:
+            if value is None or (fmt == "O" and not value):
+                continue
+            size = {"B": 1, "I": 4, "f": 4, "O": 4}[fmt]
+            self.prealign(0, size)
+            if fmt == "O":
+                self._push(struct.pack("<I", self._refer_to(value)))
+            else:
+                self._push(struct.pack("<" + fmt, value))
+            placed[fid] = self.size()
+        self.prealign(0, 4)
+        self._push(bytes(4))  # soffset, patched below
+        table_off = self.size()
+        nslots = max(placed, default=-1) + 1
+        vt = struct.pack("<HH", 4 + 2 * nslots, table_off - start)
+        for slot in range(nslots):
+            vt += struct.pack("<H", table_off - placed[slot] if slot in placed else 0)
+        for known, off in self.vtables:
+            if known == vt:
+                vt_off = off
+                break
+        else:
+            self._push(vt)
+            vt_off = self.size()
+            self.vtables.append((vt, vt_off))
+        struct.pack_into("<i", self.buf, self.size() - table_off, vt_off - table_off)
+        return table_off
+
+    def finish(self, root_off, identifier=b"memb"):
+        self.prealign(4 + len(identifier), self.minalign)
+        self._push(identifier)
+        self._push(struct.pack("<I", self._refer_to(root_off)))
+        return bytes(self.buf)
+
+
+def _finish_fbb(w, storage_type, storage_off, dim):
+    # Index: dim (u32), storage (offset), storage_type (u8) -- descending size like CreateIndex
+    root = w.table([(2, "I", dim or None), (1, "O", storage_off), (0, "B", storage_type)])
+    return w.finish(root)
+
+
+def write_trained_fbb(path, words, symbol_rows, keys, lengths, centroids):
+    """write_trained in FlatBufferBuilder order (src/trained_compression.cpp:92-100: the
+    vectors are created in the compressor, the table last)."""
+    keys = [int(k) for k in keys]
+    lengths = [int(v) for v in lengths]
+    codes = canonical_codes(lengths)
+    code_of = {k: c for k, c in zip(keys, codes)}
+    len_of = {k: v for k, v in zip(keys, lengths)}
+    packed, value_offset = bytearray(), []
+    for row in symbol_rows:
+        value_offset.append(len(packed))
+        packed += pack_row(row, code_of, len_of)
+    by_word = sorted(range(len(words)), key=lambda i: words[i])
+    packed_words, word_offsets = bytearray(), []
+    for i in by_word:
+        word_offsets.append(len(packed_words))
+        packed_words += words[i] + b"\0"
+    w = _BackWriter()
+    # decoder and clusterizer first (children), as save() is called before CreateTrained
+    dec_keys = w.vector(np.array(keys, np.uint8), 1)
+    dec_sizes = w.vector(np.array(size_offsets_from_lengths(lengths), np.uint32), 4)
+    decoder = w.table([(0, "O", dec_keys), (1, "O", dec_sizes)])
+    cents = w.vector(np.asarray(centroids, np.float32), 4)
+    clusterizer = w.table([(0, "O", cents)])
+    wo = w.vector(np.array(word_offsets, np.uint32), 4)
+    vo = w.vector(np.array([value_offset[i] for i in by_word], np.uint32), 4)
+    pw = w.string(bytes(packed_words))
+    pv = w.vector(np.frombuffer(bytes(packed), np.uint8), 1)
+    storage = w.table([(0, "O", wo), (1, "O", vo), (2, "O", pw), (3, "O", pv), (4, "O", decoder), (5, "O", clusterizer)])
+    dim = len(symbol_rows[0]) if len(symbol_rows) else 0
+    with open(path, "wb") as f:
+        f.write(_finish_fbb(w, 3, storage, dim))
+    return [words[i] for i in by_word]
+
+
+def write_uniform_fbb(path, words, mins, maxs, values, levels):
+    """write_uniform in FlatBufferBuilder order: every node is finished when its word is added
+    (src/uniform_compression.cpp:10-34), the sorted vector and the table at finalize."""
+    values = np.asarray(values, np.uint8)
+    w = _BackWriter()
+    nodes = {}
+    for i in range(len(words)):  # insertion order
+        word = w.string(words[i])
+        vals = w.vector(values[i], 1)
+        mn, mx = float(mins[i]), float(maxs[i])
+        vec = w.table([(0, "f", mn if mn != 0.0 else None), (1, "f", mx if mx != 0.0 else None), (2, "O", vals)])
+        nodes[i] = w.table([(0, "O", word), (1, "O", vec)])
+    by_word = sorted(range(len(words)), key=lambda i: words[i])
+    vector = w.offset_vector([nodes[i] for i in by_word])
+    storage = w.table([(0, "O", vector), (1, "B", levels or None)])
+    with open(path, "wb") as f:
+        f.write(_finish_fbb(w, 2, storage, values.shape[1]))
+    return [words[i] for i in by_word]
+
+
+def write_full_fbb(path, words, matrix):
+    matrix = np.asarray(matrix, np.float32)
+    w = _BackWriter()
+    nodes = {}
+    for i in range(len(words)):
+        word = w.string(words[i])
+        vals = w.vector(matrix[i], 4)
+        nodes[i] = w.table([(0, "O", word), (1, "O", vals)])
+    by_word = sorted(range(len(words)), key=lambda i: words[i])
+    vector = w.offset_vector([nodes[i] for i in by_word])
+    storage = w.table([(0, "O", vector)])
+    with open(path, "wb") as f:
+        f.write(_finish_fbb(w, 1, storage, matrix.shape[1]))
+    return [words[i] for i in by_word]

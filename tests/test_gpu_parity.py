@@ -141,6 +141,20 @@ def test_trained_edge_codes(abi, oracle, workdir):
             reader.close()
 
 
+def test_flatbufferbuilder_layout_on_gpu(abi, oracle, workdir):
+    """Files in real FlatBufferBuilder order (tests/test_host.py::_fbb_files) through the CUDA path."""
+    from test_host import _fbb_files
+
+    words, paths, _ = _fbb_files(workdir)
+    query = [w.decode() for w in words] + ["o", "", "zzz"]
+    for path in paths.values():
+        reader, want = abi.open_checked(path), oracle.open(path)
+        assert reader.keys() == want.keys()
+        assert bits_equal(reader.lookup_words(query), want.batch_embedding(query))
+        assert bits_equal(reader.decode_range(0, len(words)), want.decode_range(0, len(words)))
+        reader.close()
+
+
 @pytest.mark.parametrize("bits", [1, 4, 6, 8])
 def test_trained_kernel_variants(abi, oracle, synthetic, bits):
     """The same table through every trained path: whole-row kernel on fixed-stride records

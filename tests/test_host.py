@@ -319,3 +319,55 @@ def test_converter_cli_matches_the_builder(oracle, workdir):
     assert "items are discarded" in run.stdout and oracle.open(str(cli)).rows == len(words)
     with pytest.raises(SystemExit):
         converter.parse_args(["--from", "a", "--to", "b", "--quantization", "lossless"])
+
+
+def _fbb_files(workdir):
+    """Files in the layout a real flatbuffers::FlatBufferBuilder emits (children before parents,
+    shared vtables reached through negative soffsets, omitted defaults, root near the front)."""
+    import membfile_py
+
+    rng = np.random.default_rng(5)
+    words = [b"the", b"th", b"tho", b"a", b"zz", "été".encode(), b"m", b"o0"]
+    n, dim = len(words), 12
+    values = rng.integers(0, 256, (n, dim)).astype(np.uint8)
+    mins = [0.0, -1.0, 0.5, 0.0, 2.0, -3.0, 0.0, 1.0]
+    maxs = [1.0, 0.0, 0.5, 0.0, 4.0, 3.0, 9.0, 1.5]
+    matrix = rng.standard_normal((n, dim)).astype(np.float32)
+    keys, lengths = [3, 1, 0, 2, 4], [1, 2, 3, 4, 4]
+    centroids = rng.standard_normal(5).astype(np.float32)
+    symbols = np.array(keys)[rng.integers(0, 5, (n, dim))]
+    paths = {k: str(workdir / ("fbb_%s.bin" % k)) for k in ("uniform", "full", "trained")}
+    membfile_py.write_uniform_fbb(paths["uniform"], words, mins, maxs, values, 255)
+    membfile_py.write_full_fbb(paths["full"], words, matrix)
+    membfile_py.write_trained_fbb(paths["trained"], words, symbols, keys, lengths, centroids)
+    expect = {"uniform": None, "full": matrix, "trained": centroids[symbols]}
+    return words, paths, expect
+
+
+def test_flatbufferbuilder_layout_is_read(abi, oracle, workdir):
+    """the two in-house writers lay buffers out front to back; a file written by memb_converter
+    (flatc 1.9.0 FlatBufferBuilder) is back to front with shared vtables and negative soffsets.  No such
+    file can be produced here (flatc is absent), so the layout is reproduced by hand."""
+    words, paths, expect = _fbb_files(workdir)
+    for kind, path in paths.items():
+        data = open(path, "rb").read()
+        root = int.from_bytes(data[0:4], "little")
+        assert data[4:8] == b"memb" and root < 64  # the root table is the last thing built: lowest address
+        reader = oracle.open(path)
+        assert reader.keys() == sorted(words)
+        got = reader.batch_embedding([w.decode() for w in words])
+        if expect[kind] is not None:
+            assert np.array_equal(got, expect[kind])
+        status, handle = abi.open(path)  # the product's parser runs before any device is touched
+        assert status in (abi.OK, abi.ERR_NO_DEVICE), abi.error()
+        if status == abi.OK:
+            abi.lib.memb_b200_close(handle)
+    # at least one table reaches its vtable through a negative soffset (a shared vtable)
+    data = open(paths["full"], "rb").read()
+    negatives = 0
+    for pos in range(8, len(data) - 4, 4):
+        soffset = int.from_bytes(data[pos:pos + 4], "little", signed=True)
+        vt = pos - soffset
+        if soffset < 0 and 0 <= vt < len(data) - 4 and data[vt:vt + 4] == b"\x08\x00\x0c\x00":
+            negatives += 1
+    assert negatives >= len(words) - 1
