@@ -400,20 +400,23 @@ void loadTrained(memb_b200_reader& r)
     r.stats.upload_ms += msSince(t0);
 
     const auto t1 = std::chrono::steady_clock::now();
-    // decode tables first: the LUT flavour fixes how the rows are re-packed.  Default: one LUT
-    // copy per shared-memory bank over min(maxLen, 9) bits, longer codes through a second-level
-    // table (src/huffman_table_decoder.h:58-93).  Option trained_lut_replicas = 1 (tests): a
-    // single copy over up to 12 bits.
+    // decode tables first: the LUT flavour fixes how the rows are re-packed.  Codes of up to 9 bits:
+    // one LUT copy per shared-memory bank (conflict-free).  Longer codes: ONE copy over up to 12
+    // bits -- measured r02 on 2 M x 300 tables, 1 M random ids: bank conflicts on the single copy
+    // cost far less than a second-level lookup in the per-symbol chain (5 bit, maxLen 10: 0.326
+    // vs 0.518 ms; 8 bit, maxLen 12: 0.426 vs 0.586 ms).  Codes longer than the LUT (13..16 bits,
+    // no Builder emits them) go through a second-level table (src/huffman_table_decoder.h:58-93).
     const uint32_t maxLen = f.code.maxLen;
+    const int64_t replicasOpt = g_optLutReplicas.load();
     uint32_t replicas, lutBits, padBits;
-    if (g_optLutReplicas.load() == 1) {
-        replicas = 1;
-        lutBits = std::max(1u, std::min(maxLen, 12u));
-        padBits = 2;
-    } else {
+    if (replicasOpt == 32 || (replicasOpt == 0 && maxLen <= 9)) {
         replicas = 32;  // entry i of lane l at i*128 + l*4
         lutBits = std::max(1u, std::min(maxLen, 9u));
         padBits = K::ROWS_PAD_BITS;
+    } else {
+        replicas = 1;
+        lutBits = std::max(1u, std::min(maxLen, 12u));
+        padBits = 2;
     }
     const bool escape = maxLen > lutBits;
     const uint32_t codebookSize = static_cast<uint32_t>(f.centroids.size());

@@ -603,6 +603,16 @@ __device__ __forceinline__ void reloadWindow(LaneDecoder& d)
     d.hi = __funnelshift_r(w1, w2, d.consumed);
 }
 
+// A code longer than the LUT is wide: second-level table indexed by the bits that follow the
+// window (src/huffman_table_decoder.h:58-93,108-116).  Deliberately NOT inlined: inlined, ptxas
+// predicates these nine instructions into every symbol of the chain (r02: 0.52 ms against
+// 0.29 ms per 1 M rows); as a call it is a branch that a warp takes only when a lane has a long code.
+__device__ __noinline__ uint32_t secondLevelEntry(uint32_t e, uint32_t lo, uint32_t padL, uint32_t lut2)
+{
+    const uint32_t idx = (e >> 16) + ((lo >> padL) & ((1u << (e & 15u)) - 1u));
+    return ldsU32(lut2 + idx * 4u);
+}
+
 // One symbol: LUT entry for the next bits of the window, window advanced by the
 // code length.  Returns the entry (symbol field in bits 16..23).
 template <bool ESCAPE>
@@ -611,10 +621,7 @@ __device__ __forceinline__ uint32_t decodeSymbol(LaneDecoder& d, const TrainedPa
     uint32_t e = ldsU32((d.lo & d.lutMask) | d.lutLane);
     if (ESCAPE) {
         if (e & 0x8000u) {
-            // a code longer than the LUT is wide: second-level table indexed by the bits that
-            // follow the window (src/huffman_table_decoder.h:58-93,108-116)
-            const uint32_t idx = (e >> 16) + ((d.lo >> d.padL) & ((1u << (e & 15u)) - 1u));
-            e = ldsU32(d.lut2 + idx * 4u);
+            e = secondLevelEntry(e, d.lo, d.padL, d.lut2);
         }
     }
     d.lo = __funnelshift_r(d.lo, d.hi, e);  // shift = e & 31 = code length

@@ -109,6 +109,7 @@ struct RowsLane {
     uint32_t lo, hi;     // window: bit 0 of lo = bit `consumed` of the record
     uint32_t consumed;
     uint32_t accLo, accHi, fill8;  // symbol fields not yet stored: fill8 / 8 of them, first in bits 0..7 of accLo
+    uint32_t mul;        // 1 << fill8
     uint32_t tilePtr;    // next word of the lane's tile row
 };
 
@@ -151,16 +152,29 @@ __device__ __forceinline__ void rowsStep(RowsLane& d, uint32_t lutLane, uint32_t
     d.lo = __funnelshift_r(d.lo, d.hi, e);  // shift = e & 31
     d.hi = __funnelshift_r(d.hi, 0u, e);
     d.consumed += e & 31u;
+    // the (up to three) symbol fields join the pending 64-bit word at byte fill8 / 8.  The bits
+    // never overlap, so "or in, shifted" is a multiply-add by 1 << fill8: two IMADs on the FMA
+    // pipe instead of two shifts and two ORs on the ALU pipe, which ncu showed to be the busy one
+    // (62 % with math_pipe_throttle stalls, r02)
     const uint32_t syms = e >> 8;
-    d.accLo |= syms << d.fill8;
-    d.accHi |= __funnelshift_l(syms, 0u, d.fill8);
+    d.accLo = syms * d.mul + d.accLo;
+    d.accHi = __umulhi(syms, d.mul) + d.accHi;
     const uint32_t fill = d.fill8 + ((e >> 2) & 0x18u);  // <= 24 + 24
-    const bool full = fill >= 32u;
-    stsU32If(full && d.tilePtr < tileEnd, d.tilePtr, d.accLo);
-    d.accLo = full ? d.accHi : d.accLo;
-    d.accHi = full ? 0u : d.accHi;
-    d.tilePtr += (fill >> 3) & 4u;
+    asm volatile(
+        "{\n"
+        ".reg .pred full, store;\n"
+        "setp.ge.u32 full, %3, 32;\n"
+        "setp.lt.and.u32 store, %2, %4, full;\n"
+        "@store st.shared.u32 [%2], %0;\n"
+        "@full mov.u32 %0, %1;\n"
+        "@full mov.u32 %1, 0;\n"
+        "@full add.u32 %2, %2, 4;\n"
+        "}\n"
+        : "+r"(d.accLo), "+r"(d.accHi), "+r"(d.tilePtr)
+        : "r"(fill), "r"(tileEnd)
+        : "memory");
     d.fill8 = fill & 31u;
+    d.mul = 1u << d.fill8;
 }
 
 // Cursor of a lane over the tile's output units: unit (rr, seg, c) = 16 B unit c of reader
@@ -452,6 +466,7 @@ trained_rows_kernel(const RowsParams P, const int32_t* __restrict__ ids, uint64_
             RowsLane d;
             d.consumed = 0;
             d.accLo = d.accHi = d.fill8 = 0;
+            d.mul = 1;
             const uint32_t tileRow = tiles0 + rd.tileOffset + lane * rd.tileStride;
             // a lane without a row (missing word) decodes nothing and fills its tile row with the
             // symbol of the codebook's +0.0 slot: the flush needs no per-row predicate
