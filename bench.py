@@ -563,7 +563,14 @@ def run_b200(args):
     if args.quick:
         if rank == 0:
             frac = n * bytes_per_row / (ms_step / 1e3) / 1e9 / peak
-            print(json.dumps({"quick": True, "ids": args.ids, "options": args.option, "ms_per_step": ms_step,
+            whole = torch.empty((rows, dim), dtype=torch.float32, device=device)
+            full_ms = ctx["timer"].ms(lambda: impl.decode_range_into(0, rows, whole.data_ptr(), True, stream), reps=10)
+            odd_ms = ctx["timer"].ms(lambda: impl.decode_range_into(7, rows, whole.data_ptr(), True, stream), reps=10)
+            want_tail = np.empty((5000, dim), np.float32)
+            oracle.lib.oracle_decode_range(oracle.h, rows - 5000, rows, want_tail.ctypes.data)
+            parity_device = parity_device and same_bits(want_tail, whole[rows - 5007:rows - 7].cpu().numpy())
+            print(json.dumps({"quick": True, "full_vocab_ms": full_ms, "full_vocab_from_row_7_ms": odd_ms,
+                              "full_vocab_frac": rows * (bytes_per_row - 4) / (full_ms / 1e3) / 1e9 / peak, "ids": args.ids, "options": args.option, "ms_per_step": ms_step,
                               "rows_per_s": value, "roofline_frac": frac, "parity_sample": parity_device, "clocks": clocks,
                               "gpu_launches": int(launches)}), file=_JSON_OUT, flush=True)
         if world > 1:

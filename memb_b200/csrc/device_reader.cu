@@ -35,6 +35,7 @@ std::atomic<int64_t> g_optSymAverage{1};
 std::atomic<int64_t> g_optUniformRows{1};
 std::atomic<int64_t> g_optTrainedRows{1};   // trained_rows_kernel: 0 never, 1 unions of trained readers (one launch), 2 single lookups too
 std::atomic<int64_t> g_optRowsWarps{0};     // cap on resident warps of trained_rows_kernel (0 = as many as fit)
+std::atomic<int64_t> g_optTma{1};           // ring kernel bulk-async staging: 0 off, 1 range decodes (one copy per tile), 2 also one copy per row
 std::atomic<int64_t> g_optFixedRecords{1};  // 0: keep the offset table even when fixed-stride records would be cheap  // dense uniform lookups: 0 element walk, 1 uniform_rows_kernel unless levels is a power of two, 2 always
 
 struct StatusError {
@@ -179,6 +180,7 @@ struct memb_b200_reader {
         bool escape = false;
     };
     RowsFlavour rowsFlavour[2];
+    bool trainedTma = false;    // fixed-stride records: the ring kernel may stage rows with cp.async.bulk
     bool rowsOk = false;        // the table can go through trained_rows_kernel
     uint32_t rowsFieldShift = 0, rowsZeroWord = 0;
     uint32_t lut2Entries = 0;   // second-level entries of the ring kernel's LUT
@@ -494,6 +496,22 @@ void loadTrained(memb_b200_reader& r)
         CUDA_CHECK(cudaGetLastError());
     }
 
+    // the same records interleaved per 32 rows: a range decode stages a tile with one bulk copy
+    K::RowUnit* dBlobTiled = nullptr;
+    if (fixed && rows && g_optTma.load()) {
+        const uint64_t groups = (uint64_t(rows) + 31) / 32;
+        const uint64_t tiledWords = groups * 32 * recUnits * K::TRAINED_UNIT_WORDS;
+        CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&dBlobTiled), tiledWords * 4));
+        r.stats.device_bytes += tiledWords * 4;
+        r.owned.push_back(dBlobTiled);
+        K::interleave_records_kernel<<<static_cast<unsigned>(std::min<uint64_t>((tiledWords + 255) / 256, uint64_t(r.numSMs) * 32)),
+                                       256, 0, r.stream>>>(reinterpret_cast<const uint32_t*>(dBlob), rows,
+                                                           recUnits * K::TRAINED_UNIT_WORDS,
+                                                           reinterpret_cast<uint32_t*>(dBlobTiled), tiledWords);
+        ++g_launches;
+        CUDA_CHECK(cudaGetLastError());
+    }
+
     std::vector<uint32_t> lut2;
     const std::vector<uint32_t> lut = buildLut(f.code, lutBits, symShift, lut2);
     if (lut2.size() > K::ROWS_LUT2_MAX_ENTRIES) {
@@ -506,6 +524,7 @@ void loadTrained(memb_b200_reader& r)
 
     K::TrainedParams& p = r.trained;
     p.blob = dBlob;
+    p.blobTiled = dBlobTiled;
     p.rowOff16 = dRowOff16;
     p.recUnits = fixed ? recUnits : 0u;
     p.lut = dLut;
@@ -529,6 +548,8 @@ void loadTrained(memb_b200_reader& r)
     r.trainedEscape = escape;
     // symbols per window reload: G * maxLen <= 64 - padBits valid bits
     const uint32_t allowed = (64 - padBits) / std::max(maxLen, 1u);
+    // (re-centring the window inside the long-code branch would allow G = 4 there; measured r02 on the
+    // 16-bit-code table: 0.501 ms against 0.474 ms with plain G = 3 -- the branch body is inlined 32 times)
     r.trainedG = escape ? 3 : allowed >= 16 ? 16 : allowed >= 8 ? 8 : allowed >= 7 ? 7 : allowed >= 6 ? 6 : 5;
 
     // ---- trained_rows_kernel: multi-symbol LUT images, 9 bits wide for one reader, 8 for unions ----
@@ -567,7 +588,8 @@ void loadTrained(memb_b200_reader& r)
     // how many warps (tiles in flight) fit beside the tables in the shared window
     r.smemBase = probeSmemBase(r.stream);
     const uint32_t lutBytes = K::trainedLutBytes(lutBits, replicas);
-    const uint32_t perWarp = K::trainedWarpBytes(p.rowWords);
+    r.trainedTma = fixed;
+    const uint32_t perWarp = K::trainedWarpBytes(p.rowWords, fixed ? K::trainedLandingBytes(p.recUnits) : 0u);
     uint32_t warps = 0;
     for (uint32_t w = 1; w <= K::TRAINED_MAX_WARPS; ++w) {
         const K::TrainedLayout lay = K::trainedLayout(r.smemBase, lutBytes, perWarp, w, p.lut2Entries);
@@ -676,13 +698,14 @@ bool vec4Ok(uint32_t dim, const K::OutputSpec& o)
            reinterpret_cast<uintptr_t>(o.out) % 16 == 0;
 }
 
-template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW, bool SIDE = false, int SYM = 0>
+template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW, bool SIDE = false, int SYM = 0, int TMA = 0>
 void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBegin, uint64_t n,
                          const K::OutputSpec& o, int epi, cudaStream_t stream)
 {
     const K::TrainedParams& p = r.trained;
-    const K::TrainedLayout lay = K::trainedLayout(r.smemBase, K::trainedLutBytes(p.lutBits, p.lutReplicas),
-                                                  K::trainedWarpBytes(p.rowWords), r.trainedWarps, p.lut2Entries);
+    const K::TrainedLayout lay = K::trainedLayout(
+        r.smemBase, K::trainedLutBytes(p.lutBits, p.lutReplicas),
+        K::trainedWarpBytes(p.rowWords, TMA ? K::trainedLandingBytes(p.recUnits) : 0u), r.trainedWarps, p.lut2Entries);
     const size_t smemBytes = lay.end - r.smemBase;
     const uint64_t tiles = (n + 31) / 32;
     const unsigned grid = static_cast<unsigned>(
@@ -691,8 +714,17 @@ void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t
     if (tiles + 4ull * grid * r.trainedWarps >= 0xffffffffull) {
         fail(MEMB_B200_ERR_ARGUMENT, "decode: too many rows in one call");
     }
-    auto kernel = K::trained_decode_kernel<G, VEC4, ESCAPE, SMALLCB, RMW, SIDE, SYM>;
-    CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemBytes)));
+    auto kernel = K::trained_decode_kernel<G, VEC4, ESCAPE, SMALLCB, RMW, SIDE, SYM, TMA>;
+    {
+        // once per instantiation and device: the opt-in maximum (a per-launch size could be undercut
+        // by another thread's launch of the same instantiation for another reader)
+        static std::atomic<uint64_t> configured{0};
+        const uint64_t bit = 1ull << (r.device & 63);
+        if (!(configured.load() & bit)) {
+            CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(r.smemOptin)));
+            configured |= bit;
+        }
+    }
     uint32_t* counter = r.dTileCounters + (const_cast<memb_b200_reader&>(r).launchSeq++ % memb_b200_reader::TILE_COUNTERS);
     CUDA_CHECK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), stream));
     kernel<<<grid, block, smemBytes, stream>>>(p, ids, rowBegin, n, o, epi, counter);
@@ -914,6 +946,21 @@ void launchTrainedVec(const memb_b200_reader& r, const int32_t* ids, uint32_t ro
     if (!rmw && (o.sideHead || o.sideTail)) {
         small ? launchTrainedKernel<G, true, false, true, false, true>(r, ids, rowBegin, n, o, epi, stream)
               : launchTrainedKernel<G, true, false, false, false, true>(r, ids, rowBegin, n, o, epi, stream);
+        return;
+    }
+    if (!rmw && r.trainedTma && !ids && rowBegin % 32 == 0 && r.trained.blobTiled && g_optTma.load()) {
+        // range decode from a tile boundary: one bulk copy per tile out of the interleaved records
+        small ? launchTrainedKernel<G, true, false, true, false, false, 0, 2>(r, ids, rowBegin, n, o, epi, stream)
+              : launchTrainedKernel<G, true, false, false, false, false, 0, 2>(r, ids, rowBegin, n, o, epi, stream);
+        return;
+    }
+    if (!rmw && r.trainedTma &&
+        (g_optTma.load() == 2 || (g_optTma.load() == 1 && r.trained.recUnits > K::TRAINED_PREFETCH_UNITS))) {
+        // one bulk copy per ROW: slower than the register path for records that fit the prefetch
+        // registers (4 bit: 0.305 vs 0.296 ms per 1 M random ids), faster for longer ones, whose
+        // tail the register path fetches at staging time (8 bit, 272 B records: 0.401 vs 0.440 ms)
+        small ? launchTrainedKernel<G, true, false, true, false, false, 0, 1>(r, ids, rowBegin, n, o, epi, stream)
+              : launchTrainedKernel<G, true, false, false, false, false, 0, 1>(r, ids, rowBegin, n, o, epi, stream);
         return;
     }
     if (small) {
@@ -1247,6 +1294,8 @@ memb_b200_status memb_b200_set_option(const char* name, int64_t value)
             g_optTrainedRows = value;
         } else if (key == "trained_rows_warps" && value >= 0 && value <= K::ROWS_MAX_WARPS) {
             g_optRowsWarps = value;
+        } else if (key == "trained_tma" && value >= 0 && value <= 2) {
+            g_optTma = value;
         } else if (key == "trained_fixed_records" && (value == 0 || value == 1)) {
             g_optFixedRecords = value;
         } else if (key == "host_pass_rows" && value >= 0) {

@@ -300,6 +300,20 @@ __global__ void repack_rows_kernel(const uint8_t* __restrict__ packed, uint64_t 
     }
 }
 
+// L0c.  Fixed-stride records once more, interleaved per group of 32 rows (TrainedParams::blobTiled):
+// output word o = (g * recWords + w) * 32 + l holds word w of row 32 g + l (zero past the last row).
+__global__ void interleave_records_kernel(const uint32_t* __restrict__ blob, uint32_t rows, uint32_t recWords,
+                                          uint32_t* __restrict__ tiled, uint64_t totalWords)
+{
+    for (uint64_t o = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; o < totalWords;
+         o += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+        const uint64_t group = o / (recWords * 32u);
+        const uint32_t rem = static_cast<uint32_t>(o - group * (recWords * 32u));
+        const uint64_t row = group * 32u + (rem & 31u);
+        tiled[o] = row < rows ? blob[row * recWords + (rem >> 5)] : 0u;
+    }
+}
+
 __global__ void pad_rows16_kernel(const uint32_t* __restrict__ rowBytes, uint32_t rows,
                                   uint32_t* __restrict__ rowUnits)
 {
@@ -351,6 +365,9 @@ __global__ void pad_rows16_kernel(const uint32_t* __restrict__ rowBytes, uint32_
 // streaming store covering 128 contiguous bytes per 8 lanes.
 struct TrainedParams {
     const RowUnit* blob;
+    const RowUnit* blobTiled;   // fixed-stride records once more, interleaved per group of 32 rows: word w of row
+                                // 32 g + l at word (g * recUnits * 4 + w) * 32 + l -- the staged layout itself, so a
+                                // range decode stages a whole tile with ONE bulk copy (nullptr: not built)
     const uint32_t* rowOff16;   // (name from the 16 B layout) rows+1 offsets into blob in UNITS; unused when recUnits != 0
     uint32_t recUnits;          // != 0: fixed-stride records, row r at blob + r * recUnits (no offset table)
     const uint32_t* lut;
@@ -399,9 +416,17 @@ __host__ __device__ inline uint32_t trainedLutBytes(uint32_t lutBits, uint32_t r
 {
     return (4u << lutBits) * replicas;
 }
-__host__ __device__ inline uint32_t trainedWarpBytes(uint32_t rowWords)
+// per warp: staged rows (bank-per-lane), symbol tile, and -- bulk-async staging (TMA) -- the
+// landing buffer the warp's 32 records are copied into by cp.async.bulk
+// (sized like the staged rows themselves, window slack included: in the tiled mode it IS a
+// second staged-rows buffer)
+__host__ __device__ inline uint32_t trainedLandingBytes(uint32_t recUnits)
 {
-    return rowWords * 128 + TRAINED_TILE_BYTES;
+    return (recUnits * TRAINED_UNIT_WORDS + 4u) * 128u;
+}
+__host__ __device__ inline uint32_t trainedWarpBytes(uint32_t rowWords, uint32_t landingBytes = 0)
+{
+    return rowWords * 128 + TRAINED_TILE_BYTES + landingBytes;
 }
 
 // Where things live in the CTA's shared window, as ABSOLUTE shared addresses
@@ -409,6 +434,7 @@ __host__ __device__ inline uint32_t trainedWarpBytes(uint32_t rowWords)
 struct TrainedLayout {
     uint32_t codebook;   // 1 KiB aligned
     uint32_t lut2;       // second-level entries, right after the codebooks
+    uint32_t mbar;       // one mbarrier per warp (bulk-async staging)
     uint32_t lut;        // aligned to lutBytes
     uint32_t lowStart;   // warps [0, lowWarps) at lowStart + w * perWarp
     uint32_t lowWarps;
@@ -421,7 +447,8 @@ __host__ __device__ inline TrainedLayout trainedLayout(uint32_t base, uint32_t l
     TrainedLayout l;
     l.codebook = (base + 1023u) & ~1023u;
     l.lut2 = l.codebook + TRAINED_CODEBOOK_BYTES;
-    l.lowStart = (l.lut2 + lut2Entries * 4u + 127u) & ~127u;
+    l.mbar = (l.lut2 + lut2Entries * 4u + 7u) & ~7u;
+    l.lowStart = (l.mbar + 8u * TRAINED_MAX_WARPS + 127u) & ~127u;
     l.lut = (l.lowStart + lutBytes - 1) / lutBytes * lutBytes;
     const uint32_t fit = (l.lut - l.lowStart) / perWarp;
     l.lowWarps = fit < warps ? fit : warps;
@@ -523,6 +550,53 @@ __device__ __forceinline__ void stcsF4(void* ptr, float4 v)
 {
     asm volatile("st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(ptr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
                  : "memory");
+}
+
+// ---- mbarrier + 1-D bulk copy (cp.async.bulk, the non-tensor TMA path) ----
+__device__ __forceinline__ void mbarInit(uint32_t mbar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbarExpectTx(uint32_t mbar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbarWait(uint32_t mbar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "MEMB_MBAR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra MEMB_MBAR_DONE;\n"
+        "bra MEMB_MBAR_WAIT;\n"
+        "MEMB_MBAR_DONE:\n"
+        "}\n" ::"r"(mbar),
+        "r"(parity)
+        : "memory");
+}
+// 1-D bulk copy global -> shared (bytes a multiple of 16, both addresses 16 B aligned),
+// completion counted on the mbarrier.  SASS: UBLKCP.S.G
+__device__ __forceinline__ void bulkLoad(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(mbar)
+                 : "memory");
+}
+
+// all earlier generic-proxy accesses of this thread to shared memory are ordered before its later
+// async-proxy operations (a bulk copy that overwrites a buffer the thread has just read)
+__device__ __forceinline__ void fenceProxyAsync()
+{
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ RowUnit ldsRowUnit(uint32_t addr)
+{
+    RowUnit v;
+    static_assert(TRAINED_UNIT_WORDS == 4, "bulk-async staging is written for 16 B units");
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.w[0]), "=r"(v.w[1]), "=r"(v.w[2]), "=r"(v.w[3]) : "r"(addr));
+    return v;
 }
 
 // Four centroids for the four symbol fields packed in s4.  cb = shared address of
@@ -745,7 +819,16 @@ __device__ __forceinline__ uint32_t shflFrom(uint32_t v, uint32_t srcLane)
 // SIDE: the launch redirects first / last units to side buffers (OutputSpec::sideHead).
 // SYM: 1 = the launch stores symbol words instead of fp32 rows, 2 = the running sum it adds to
 // is gathered from another reader's symbol words (OutputSpec::sym).
-template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW, bool SIDE, int SYM>
+// TMA: the warp's 32 records reach shared memory through cp.async.bulk (one 1-D bulk copy per
+// lane into a landing buffer, completion on the warp's mbarrier), a tile ahead, instead of
+// through 128-bit loads into registers: no gathered LDG in the LSU pipe, no prefetch registers.
+// Needs fixed-stride records (TrainedParams::recUnits).  Measured r02 (1 M rows, 2.2 M x 300 4-bit):
+// 32 bulk copies of 144 B per tile are SLOWER than the register path (0.305 vs 0.296 ms random,
+// 0.304 vs 0.277 ms sequential): the copy engine's per-operation cost, not bytes, is the limit.
+// TMA == 2 (range decodes whose first row is a multiple of 32): the tile's 32 rows are one
+// contiguous block of TrainedParams::blobTiled, already in the staged layout -- ONE bulk copy per
+// tile straight into a second staged-rows buffer, no copy-out, no row ids.
+template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW, bool SIDE, int SYM, int TMA = 0>
 __global__ void __maxnreg__(TRAINED_MAX_REGS)
 trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, uint32_t rowBegin, uint64_t n,
                       const OutputSpec o, const int epi, uint32_t* __restrict__ tileCounter)
@@ -757,7 +840,8 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
 
     const uint32_t lutBytes = trainedLutBytes(p.lutBits, p.lutReplicas);
     const uint32_t base = smemAddr(smem);
-    const TrainedLayout lay = trainedLayout(base, lutBytes, trainedWarpBytes(p.rowWords), warpsPerCta, p.lut2Entries);
+    const uint32_t perWarp = trainedWarpBytes(p.rowWords, TMA ? trainedLandingBytes(p.recUnits) : 0u);
+    const TrainedLayout lay = trainedLayout(base, lutBytes, perWarp, warpsPerCta, p.lut2Entries);
     {
         uint32_t dynBytes;
         asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dynBytes));
@@ -813,10 +897,12 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
 
     // shared-window addresses
     const uint32_t cb = lay.codebook;
-    const uint32_t warpBase = warp < lay.lowWarps
-                                  ? lay.lowStart + warp * trainedWarpBytes(p.rowWords)
-                                  : lay.highStart + (warp - lay.lowWarps) * trainedWarpBytes(p.rowWords);
+    const uint32_t warpBase = warp < lay.lowWarps ? lay.lowStart + warp * perWarp
+                                                  : lay.highStart + (warp - lay.lowWarps) * perWarp;
     const uint32_t tile = warpBase + p.rowWords * 128;  // 32 rows x 132 B of symbols (ring of two chunks)
+    const uint32_t landing = tile + TRAINED_TILE_BYTES;  // TMA: record of lane l at + l * recBytes
+    const uint32_t recBytes = p.recUnits * TRAINED_UNIT_BYTES;
+    const uint32_t mbar = lay.mbar + warp * 8u;
     LaneDecoder d;
     d.lutLane = lay.lut | (p.lutReplicas == 1 ? 0u : lane * 4u);
     d.lutMask = p.lutMask;
@@ -907,30 +993,111 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
             : "memory");
     };
     drawTicket();
-    uint32_t offLo, offHi, offLoNext, offHiNext;
+    uint32_t offLo = 0, offHi = 0, offLoNext = 0, offHiNext = 0;
     bool hasRow;
     uint32_t rowAfter = fetchId(t, hasRow);
-    bool present = fetchOffsets(rowAfter, hasRow, offLo, offHi);
-    rowAfter = fetchId(t1, hasRow);
-    bool presentNext = fetchOffsets(rowAfter, hasRow, offLoNext, offHiNext);
-    rowAfter = fetchId(t2, hasRow);
-    uint32_t o16 = offLo, units = offHi - offLo;
-    prefetchRows(o16, units);
+    bool present, presentNext;
+    uint32_t o16 = 0, units = 0, mbarPhase = 0;
+    // TMA: every lane copies its own record (record 0 for a lane without a row) into the landing
+    // buffer; lane 0 arms the warp's mbarrier with the 32 records' bytes first
+    auto issueRecords = [&](uint32_t row, bool ok) {
+        if (lane == 0) {
+            mbarExpectTx(mbar, 32u * recBytes);
+        }
+        __syncwarp();
+        bulkLoad(landing + lane * recBytes, p.blob + static_cast<uint64_t>(ok ? row : 0u) * p.recUnits, recBytes, mbar);
+    };
+    const uint32_t rowsBuffer = d.rowLane;  // TMA == 2: the decode alternates between this and the landing buffer
+    uint32_t tiledBuffer = 0;
+    auto issueTile = [&](uint32_t tt, uint32_t buffer) {
+        if (lane == 0 && tt < numTiles) {
+            const uint32_t bytes = p.recUnits * (TRAINED_UNIT_BYTES * 32u);
+            mbarExpectTx(mbar, bytes);
+            bulkLoad(buffer ? landing : warpBase,
+                     p.blobTiled + (static_cast<uint64_t>(rowBegin >> 5) + tt) * (p.recUnits * 32u), bytes, mbar);
+        }
+    };
+    if (TMA == 2) {
+        if (lane == 0) {
+            mbarInit(mbar, 1);
+        }
+        __syncwarp();
+        issueTile(t, 0);
+        present = hasRow && rowAfter < p.rows;
+        presentNext = false;
+    } else if (TMA) {
+        // pipeline: tile t+2 row id, tile t+1 records in flight (bulk copies), tile t decode
+        if (lane == 0) {
+            mbarInit(mbar, 1);
+        }
+        __syncwarp();
+        present = hasRow && rowAfter < p.rows;
+        issueRecords(rowAfter, present);
+        rowAfter = fetchId(t1, hasRow);
+        presentNext = false;
+    } else {
+        present = fetchOffsets(rowAfter, hasRow, offLo, offHi);
+        rowAfter = fetchId(t1, hasRow);
+        presentNext = fetchOffsets(rowAfter, hasRow, offLoNext, offHiNext);
+        rowAfter = fetchId(t2, hasRow);
+        o16 = offLo;
+        units = offHi - offLo;
+        prefetchRows(o16, units);
+    }
 
     while (t < numTiles) {
         // The ticket drawn a tile ago is redeemed BEFORE this tile's loads are
         // issued: ncu r01 showed the shuffle waiting on the scoreboard it shared
         // with the loads issued just ahead of it (10 % of all stall samples).
-        const uint32_t t4 = 4u * totalWarps + shflFrom(ticket, ticketLane);
+        const uint32_t t4 = (TMA ? 3u : 4u) * totalWarps + shflFrom(ticket, ticketLane);
         const uint32_t presentMask = __ballot_sync(0xffffffffu, present);
+        if (TMA == 2) {
+            // ---- the tile has landed in the staged layout; the next one goes to the other buffer ----
+            mbarWait(mbar, mbarPhase);
+            mbarPhase ^= 1u;
+            d.rowLane = tiledBuffer ? landing + lane * 4u : rowsBuffer;
+            tiledBuffer ^= 1u;
+            fenceProxyAsync();  // (the other buffer was read by the previous tile's decode, which ended in a __syncwarp)
+            issueTile(t1, tiledBuffer);
+            drawTicket();
+            rowAfter = fetchId(t1, hasRow);
+            presentNext = hasRow && rowAfter < p.rows;
+        } else if (TMA) {
+            // ---- the records have landed: own record -> own bank; then the next tile's copies ----
+            mbarWait(mbar, mbarPhase);
+            mbarPhase ^= 1u;
+            for (uint32_t k0 = 0; k0 < p.recUnits; k0 += 4) {
+                RowUnit c[4];
+#pragma unroll
+                for (uint32_t k = 0; k < 4; ++k) {
+                    if (k0 + k < p.recUnits) {
+                        c[k] = ldsRowUnit(landing + lane * recBytes + (k0 + k) * TRAINED_UNIT_BYTES);
+                    }
+                }
+#pragma unroll
+                for (uint32_t k = 0; k < 4; ++k) {
+                    if (k0 + k < p.recUnits) {
+                        stageRowUnit(d.rowLane + (k0 + k) * (TRAINED_UNIT_WORDS * 128), c[k]);
+                    }
+                }
+            }
+            fenceProxyAsync();
+            __syncwarp();
+            presentNext = hasRow && rowAfter < p.rows;
+            issueRecords(rowAfter, presentNext);
+            drawTicket();
+            rowAfter = fetchId(t2, hasRow);
+        }
         // ---- stage: own row -> own bank ----
+        if (!TMA) {
 #pragma unroll
         for (uint32_t k = 0; k < TRAINED_PREFETCH_UNITS; ++k) {
             if (k < units) {
                 stageRowUnit(d.rowLane + k * (TRAINED_UNIT_WORDS * 128), pre[k]);
             }
         }
-        {
+        }
+        if (!TMA) {
             // rows longer than the prefetch window: the rest comes straight from HBM
             const RowUnit* src = p.blob + o16;
             const uint32_t unitsMax = __reduce_max_sync(0xffffffffu, presentMask ? units : 0u);
@@ -951,12 +1118,16 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
             }
         }
         // advance the pipeline: ticket of t+4, rows of t+1, offsets of t+2, id of t+3
-        drawTicket();
-        const uint32_t o16Next = offLoNext, unitsNext = offHiNext - offLoNext;
-        prefetchRows(o16Next, unitsNext);
-        uint32_t offLoAfter, offHiAfter;
-        const bool presentAfter = fetchOffsets(rowAfter, hasRow, offLoAfter, offHiAfter);
-        rowAfter = fetchId(t3, hasRow);
+        uint32_t o16Next = 0, unitsNext = 0, offLoAfter = 0, offHiAfter = 0;
+        bool presentAfter = false;
+        if (!TMA) {
+            drawTicket();
+            o16Next = offLoNext;
+            unitsNext = offHiNext - offLoNext;
+            prefetchRows(o16Next, unitsNext);
+            presentAfter = fetchOffsets(rowAfter, hasRow, offLoAfter, offHiAfter);
+            rowAfter = fetchId(t3, hasRow);
+        }
 
         d.hi = d.lo = 0;
         d.consumed = 0;
@@ -1195,15 +1366,24 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
             __syncwarp();
         }
         present = presentNext;
-        o16 = o16Next;
-        units = unitsNext;
-        presentNext = presentAfter;
-        offLoNext = offLoAfter;
-        offHiNext = offHiAfter;
-        t = t1;
-        t1 = t2;
-        t2 = t3;
-        t3 = t4;
+        if (TMA) {
+            t = t1;
+            t1 = t2;
+            t2 = t4;
+        } else {
+            o16 = o16Next;
+            units = unitsNext;
+            presentNext = presentAfter;
+            offLoNext = offLoAfter;
+            offHiNext = offHiAfter;
+            t = t1;
+            t1 = t2;
+            t2 = t3;
+            t3 = t4;
+        }
+    }
+    if (TMA == 1) {
+        mbarWait(mbar, mbarPhase);  // the copies issued for the tile after the last: never leave with them in flight
     }
 }
 

@@ -73,38 +73,6 @@ struct RowsParams {
     float divisor;
 };
 
-__device__ __forceinline__ void mbarInit(uint32_t mbar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbarExpectTx(uint32_t mbar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbarWait(uint32_t mbar, uint32_t parity)
-{
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "ROWS_MBAR_WAIT:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra ROWS_MBAR_DONE;\n"
-        "bra ROWS_MBAR_WAIT;\n"
-        "ROWS_MBAR_DONE:\n"
-        "}\n" ::"r"(mbar),
-        "r"(parity)
-        : "memory");
-}
-// 1-D bulk copy global -> shared (bytes a multiple of 16, both addresses 16 B aligned),
-// completion counted on the mbarrier.  SASS: UBLKCP.S.G
-__device__ __forceinline__ void bulkLoad(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar)
-{
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                 "l"(src), "r"(bytes), "r"(mbar)
-                 : "memory");
-}
-
 struct RowsLane {
     uint32_t lo, hi;     // window: bit 0 of lo = bit `consumed` of the record
     uint32_t consumed;
