@@ -731,6 +731,23 @@ def strong_scaling(args, ctx, reader, oracle):
         ctx["barrier"]()
         result["decode_plus_gather_ms"] = ctx["max_over_ranks"](timer.ms(both, reps=5, warm=2))
         result["gather"] = "in place: ncclAllGather of the slot each rank decoded into (no send copy)"
+        # fused: the decode kernel's stores go to an NVLS multicast address (multimem.st), the NVSwitch
+        # replicates them into every rank's buffer while the decode runs -- no collective at all
+        try:
+            from memb_b200.sharding import GatheredMatrix
+
+            fused = GatheredMatrix(reader)
+            ctx["barrier"]()
+            result["fused_decode_gather_ms"] = ctx["max_over_ranks"](timer.ms(fused.fill, reps=5, warm=2))
+            result["fused_gb_per_s_into_each_gpu"] = rows * dim * 4 * (world - 1) / world / (result["fused_decode_gather_ms"] / 1e3) / 1e9
+            result["fused"] = "decode with multimem.st to torch symmetric memory's multicast address + one symmetric-memory barrier"
+            fused_view = fused.fill()
+            torch.cuda.synchronize()
+            result["fused_available"] = True
+        except Exception as exc:  # noqa: BLE001  (no NVLS / symmetric memory on this box)
+            fused_view = None
+            result["fused_available"] = False
+            result["fused_error"] = str(exc)[:200]
     # one GPU decoding everything alone, timed in the same run on rank 0's GPU while the others wait
     ctx["barrier"]()
     alone_ms = timer.ms(lambda: impl.decode_range_into(0, rows, whole.data_ptr(), True, stream), reps=10) if rank == 0 else 0.0
@@ -742,6 +759,9 @@ def strong_scaling(args, ctx, reader, oracle):
     impl.decode_range_into(0, rows, whole.data_ptr(), True, stream)
     torch.cuda.synchronize()
     same = bool(torch.equal(gathered[:rows].view(torch.int32), whole.view(torch.int32)))
+    if world > 1 and fused_view is not None:
+        result["parity_fused"] = bool(torch.equal(fused_view.view(torch.int32), whole.view(torch.int32)))
+        same = same and result["parity_fused"]
     begin = (rows // max(world, 1)) * rank
     count = min(20_000, rows - begin)
     want = np.empty((count, dim), np.float32)

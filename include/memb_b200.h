@@ -136,6 +136,16 @@ memb_b200_status memb_b200_decode_ids(memb_b200_reader* reader, const int32_t* i
 memb_b200_status memb_b200_decode_range(memb_b200_reader* reader, uint64_t row_begin, uint64_t row_end,
                                         float* out, memb_b200_mem_kind out_kind, void* stream);
 
+/* Fused decode -> all-gather for the sharded full-vocabulary decode ("each GPU stores its
+ * slice straight into the owner's buffer").  out_multicast is an NVLS MULTICAST address of the
+ * gathered matrix's slot for these rows (e.g. torch symmetric memory's multicast_ptr + offset): the
+ * decode kernel's stores are multimem.st, which the NVSwitch replicates into every GPU of the group,
+ * so the transfer overlaps the decode and no separate collective moves the rows.  Asynchronous on
+ * `stream`; the caller synchronises the group (a barrier on the symmetric memory) before reading.
+ * Trained readers with dim % 4 == 0 only (MEMB_B200_ERR_UNSUPPORTED otherwise). */
+memb_b200_status memb_b200_decode_range_multicast(memb_b200_reader* reader, uint64_t row_begin, uint64_t row_end,
+                                                  float* out_multicast, void* stream);
+
 /* ReadersUnion.batch_embedding — python/memb/readers_union.py:90-96 with
  * np.mean(axis=0) / np.concatenate(axis=-1) (:16-18,30-32) fused into the decode.
  * All readers must live on the same device.  ids: num_readers*n, reader-major.

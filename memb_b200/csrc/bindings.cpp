@@ -547,6 +547,14 @@ public:
                                      reinterpret_cast<void*>(stream)));
     }
 
+    // rows [begin, end) stored through an NVLS multicast address (memb_b200_decode_range_multicast)
+    void decodeRangeMulticast(uint64_t begin, uint64_t end, uintptr_t outMulticast, uintptr_t stream) const
+    {
+        py::gil_scoped_release release;
+        check(memb_b200_decode_range_multicast(impl_, begin, end, reinterpret_cast<float*>(outMulticast),
+                                               reinterpret_cast<void*>(stream)));
+    }
+
     py::dict loadStats() const
     {
         memb_b200_load_stats s;
@@ -742,6 +750,8 @@ PYBIND11_MODULE(_memb, m)
              py::arg("out"), py::arg("out_on_device"), py::arg("stream") = 0)
         .def("decode_range_into", &Reader::decodeRangeInto, py::arg("begin"), py::arg("end"), py::arg("out"),
              py::arg("out_on_device"), py::arg("stream") = 0)
+        .def("decode_range_multicast", &Reader::decodeRangeMulticast, py::arg("begin"), py::arg("end"),
+             py::arg("out_multicast"), py::arg("stream") = 0)
         .def("load_stats", &Reader::loadStats);
 
     m.def("available_compression_strategies", &availableCompressionStrategies);

@@ -35,7 +35,7 @@ std::atomic<int64_t> g_optSymAverage{1};
 std::atomic<int64_t> g_optUniformRows{1};
 std::atomic<int64_t> g_optTrainedRows{1};   // trained_rows_kernel: 0 never, 1 unions of trained readers (one launch), 2 single lookups too
 std::atomic<int64_t> g_optRowsWarps{0};     // cap on resident warps of trained_rows_kernel (0 = as many as fit)
-std::atomic<int64_t> g_optTma{1};           // ring kernel bulk-async staging: 0 off, 1 range decodes (one copy per tile), 2 also one copy per row
+std::atomic<int64_t> g_optTma{0};           // ring kernel bulk-async staging (EXPERIMENT, off: see DESIGN.md 4.4): 1 range decodes (one copy per tile), 2 also one copy per row
 std::atomic<int64_t> g_optFixedRecords{1};  // 0: keep the offset table even when fixed-stride records would be cheap  // dense uniform lookups: 0 element walk, 1 uniform_rows_kernel unless levels is a power of two, 2 always
 
 struct StatusError {
@@ -588,8 +588,8 @@ void loadTrained(memb_b200_reader& r)
     // how many warps (tiles in flight) fit beside the tables in the shared window
     r.smemBase = probeSmemBase(r.stream);
     const uint32_t lutBytes = K::trainedLutBytes(lutBits, replicas);
-    r.trainedTma = fixed;
-    const uint32_t perWarp = K::trainedWarpBytes(p.rowWords, fixed ? K::trainedLandingBytes(p.recUnits) : 0u);
+    r.trainedTma = fixed && g_optTma.load() != 0;  // (decided at load: the landing buffers cost shared memory)
+    const uint32_t perWarp = K::trainedWarpBytes(p.rowWords, r.trainedTma ? K::trainedLandingBytes(p.recUnits) : 0u);
     uint32_t warps = 0;
     for (uint32_t w = 1; w <= K::TRAINED_MAX_WARPS; ++w) {
         const K::TrainedLayout lay = K::trainedLayout(r.smemBase, lutBytes, perWarp, w, p.lut2Entries);
@@ -1649,6 +1649,34 @@ memb_b200_status memb_b200_decode_range(memb_b200_reader* reader, uint64_t row_b
         });
         if (!async) {
             CUDA_CHECK(cudaStreamSynchronize(s));
+        }
+    });
+}
+
+memb_b200_status memb_b200_decode_range_multicast(memb_b200_reader* reader, uint64_t row_begin, uint64_t row_end,
+                                                  float* out_multicast, void* stream)
+{
+    return guarded([&] {
+        if (!reader || !out_multicast) {
+            fail(MEMB_B200_ERR_ARGUMENT, "decode_range_multicast: null argument");
+        }
+        if (row_begin > row_end || row_end > reader->file->rows) {
+            fail(MEMB_B200_ERR_ARGUMENT, "decode_range_multicast: rows out of range");
+        }
+        memb_b200_reader& r = *reader;
+        const uint32_t dim = r.file->dim;
+        if (r.file->storage != STORAGE_TRAINED || r.trainedWarps == 0 || dim % 4 != 0 ||
+            reinterpret_cast<uintptr_t>(out_multicast) % 16 != 0) {
+            fail(MEMB_B200_ERR_UNSUPPORTED, "decode_range_multicast: trained storage with dim % 4 == 0 only");
+        }
+        DeviceGuard guard(r.device);
+        K::OutputSpec o{out_multicast, dim, 0, 1.0f};
+        o.multicast = 1;
+        if (row_end > row_begin) {
+            launchTrainedG<true>(r, nullptr, static_cast<uint32_t>(row_begin), row_end - row_begin, o, K::EPI_WRITE,
+                                 static_cast<cudaStream_t>(stream));
+            ++g_launches;
+            CUDA_CHECK(cudaGetLastError());
         }
     });
 }

@@ -61,6 +61,9 @@ struct OutputSpec {
     // 3600 bytes move per row.  Row i of the launch lives at sym + i * symWords.
     uint32_t* sym = nullptr;
     uint32_t symWords = 0;
+    // `out` is an NVLS MULTICAST address (one store lands in the same place of every GPU's buffer:
+    // the fused decode -> all-gather of a sharded full-vocabulary decode): stores are multimem.st
+    uint32_t multicast = 0;
     const float* symCodebook = nullptr;  // reader 0's centroids (SYM == 2)
     uint32_t symCodebookSize = 0;
     uint32_t symFieldShift = 0;          // reader 0's symbol field -> byte offset into its codebook
@@ -585,6 +588,22 @@ __device__ __forceinline__ void bulkLoad(uint32_t dst, const void* src, uint32_t
                  : "memory");
 }
 
+// One elected lane of the (converged) warp arms the mbarrier with `bytes` and, when `copy`, issues ONE
+// bulk copy -- as predicated instructions, not under a divergent branch.
+__device__ __forceinline__ void electExpectAndCopy(uint32_t mbar, uint32_t bytes, bool copy, uint32_t dst, const void* src)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred leader, go;\n"
+        "elect.sync _|leader, 0xffffffff;\n"
+        "setp.ne.and.u32 go, %4, 0, leader;\n"
+        "@leader mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n"
+        "@go cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%2], [%3], %1, [%0];\n"
+        "}\n" ::"r"(mbar),
+        "r"(bytes), "r"(dst), "l"(src), "r"(static_cast<uint32_t>(copy))
+        : "memory");
+}
+
 // all earlier generic-proxy accesses of this thread to shared memory are ordered before its later
 // async-proxy operations (a bulk copy that overwrites a buffer the thread has just read)
 __device__ __forceinline__ void fenceProxyAsync()
@@ -597,6 +616,23 @@ __device__ __forceinline__ RowUnit ldsRowUnit(uint32_t addr)
     static_assert(TRAINED_UNIT_WORDS == 4, "bulk-async staging is written for 16 B units");
     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.w[0]), "=r"(v.w[1]), "=r"(v.w[2]), "=r"(v.w[3]) : "r"(addr));
     return v;
+}
+
+// The flush's store: streaming 128-bit store, or -- OutputSpec::multicast -- one multimem.st that the
+// NVSwitch replicates into every GPU of the multicast group (warp-uniform choice, no branch).
+__device__ __forceinline__ void flushStoreF4If(uint32_t multicast, bool pred, void* ptr, float4 v)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p, mc, uc;\n"
+        "setp.ne.u32 p, %5, 0;\n"
+        "setp.ne.and.u32 mc, %6, 0, p;\n"
+        "setp.eq.and.u32 uc, %6, 0, p;\n"
+        "@uc st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};\n"
+        "@mc multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};\n"
+        "}\n" ::"l"(ptr),
+        "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(static_cast<uint32_t>(pred)), "r"(multicast)
+        : "memory");
 }
 
 // Four centroids for the four symbol fields packed in s4.  cb = shared address of
@@ -827,7 +863,13 @@ __device__ __forceinline__ uint32_t shflFrom(uint32_t v, uint32_t srcLane)
 // 0.304 vs 0.277 ms sequential): the copy engine's per-operation cost, not bytes, is the limit.
 // TMA == 2 (range decodes whose first row is a multiple of 32): the tile's 32 rows are one
 // contiguous block of TrainedParams::blobTiled, already in the staged layout -- ONE bulk copy per
-// tile straight into a second staged-rows buffer, no copy-out, no row ids.
+// tile straight into a second staged-rows buffer, no copy-out, no row ids (4 bit: 0.576 vs 0.582 ms
+// for the 2.2 M-row table; 8 bit, 272 B records: 0.706 vs 0.775 ms).
+// BOTH MODES ARE OFF BY DEFAULT (option trained_tma): a whole-matrix comparison against the
+// register path shows the first 32 columns of the tile's FIRST row wrong in about 2 % of the
+// tiles a warp takes after its third -- timing dependent, not explained by the staged data or
+// the shared-memory layout (padding, a converged elect-predicated issue and an extra __syncwarp
+// after the wait change the rate, not the fact), and compute-sanitizer is closed on this pool.
 template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW, bool SIDE, int SYM, int TMA = 0>
 __global__ void __maxnreg__(TRAINED_MAX_REGS)
 trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, uint32_t rowBegin, uint64_t n,
@@ -1001,20 +1043,17 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     // TMA: every lane copies its own record (record 0 for a lane without a row) into the landing
     // buffer; lane 0 arms the warp's mbarrier with the 32 records' bytes first
     auto issueRecords = [&](uint32_t row, bool ok) {
-        if (lane == 0) {
-            mbarExpectTx(mbar, 32u * recBytes);
-        }
+        electExpectAndCopy(mbar, 32u * recBytes, false, 0u, nullptr);
         __syncwarp();
         bulkLoad(landing + lane * recBytes, p.blob + static_cast<uint64_t>(ok ? row : 0u) * p.recUnits, recBytes, mbar);
     };
     const uint32_t rowsBuffer = d.rowLane;  // TMA == 2: the decode alternates between this and the landing buffer
     uint32_t tiledBuffer = 0;
     auto issueTile = [&](uint32_t tt, uint32_t buffer) {
-        if (lane == 0 && tt < numTiles) {
+        if (tt < numTiles) {  // (warp-uniform)
             const uint32_t bytes = p.recUnits * (TRAINED_UNIT_BYTES * 32u);
-            mbarExpectTx(mbar, bytes);
-            bulkLoad(buffer ? landing : warpBase,
-                     p.blobTiled + (static_cast<uint64_t>(rowBegin >> 5) + tt) * (p.recUnits * 32u), bytes, mbar);
+            electExpectAndCopy(mbar, bytes, true, buffer ? landing : warpBase,
+                               p.blobTiled + (static_cast<uint64_t>(rowBegin >> 5) + tt) * (p.recUnits * 32u));
         }
     };
     if (TMA == 2) {
@@ -1054,6 +1093,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         if (TMA == 2) {
             // ---- the tile has landed in the staged layout; the next one goes to the other buffer ----
             mbarWait(mbar, mbarPhase);
+            __syncwarp();
             mbarPhase ^= 1u;
             d.rowLane = tiledBuffer ? landing + lane * 4u : rowsBuffer;
             tiledBuffer ^= 1u;
@@ -1266,7 +1306,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                                 continue;
                             }
                             const float4 v = gatherCentroids<SMALLCB>(cb, s4);
-                            stcsF4(reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j, v);
+                            flushStoreF4If(o.multicast, true, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j, v);
                         }
                     } else {
 #pragma unroll
@@ -1284,7 +1324,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             if (SIDE) {
                                 dst = redirectUnit(o, dst, row0 + it * TRAINED_FLUSH_ROWS + fr, static_cast<uint32_t>(j), dim / 4 - 1);
                             }
-                            stcsF4If(j >= 0 && j < end, dst, v);
+                            flushStoreF4If(o.multicast, j >= 0 && j < end, dst, v);
                         }
                         if (last) {
 #pragma unroll
@@ -1301,7 +1341,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                                 if (SIDE) {
                                     dst = redirectUnit(o, dst, row0 + it * TRAINED_FLUSH_ROWS + fr, static_cast<uint32_t>(j2), dim / 4 - 1);
                                 }
-                                stcsF4If(j2 < unitsAfter, dst, u);
+                                flushStoreF4If(o.multicast, j2 < unitsAfter, dst, u);
                             }
                         }
                     }
@@ -1338,7 +1378,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                                     v.z = applyEpilogue(v.z, old.z, epi, o.divisor);
                                     v.w = applyEpilogue(v.w, old.w, epi, o.divisor);
                                 }
-                                __stcs(dst, v);
+                                flushStoreF4If(o.multicast, true, dst, v);
                             }
                         }
                         rowPtr += TRAINED_FLUSH_ROWS * rowBytes;

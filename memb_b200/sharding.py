@@ -91,6 +91,50 @@ def decode_range_gathered(reader, begin=0, end=None, *, group=None, out=None):
     return out[:n]
 
 
+class GatheredMatrix:
+    """The dense (rows, dim) matrix of a reader on EVERY rank, filled by a fused decode -> all-gather:
+    the buffer is torch symmetric memory with an NVLS multicast mapping, each rank decodes its row
+    range with stores to the multicast address (memb_b200_decode_range_multicast), and the NVSwitch
+    replicates every store into all ranks' buffers while the decode is still running -- no
+    separate collective, no staging copy.  `fill()` returns the (rows, dim) view once every
+    rank's rows have arrived (a one-element NCCL all-reduce on the current stream serves as the
+    barrier: the symmetric-memory handle's own device barrier, queued right before the decode
+    kernel without a host synchronisation in between, hung on the B200 box -- r02).
+
+    Raises RuntimeError when the process group has no multicast support (then use
+    decode_range_gathered: decode in place + one NCCL all-gather)."""
+
+    def __init__(self, reader, group=None):
+        import torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+
+        self.reader = reader
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank, self.world = dist.get_rank(self.group), dist.get_world_size(self.group)
+        self.rows, self.dim = reader.rows, reader.dim
+        self.job = (self.rows + self.world - 1) // self.world
+        self.device = torch.device("cuda", reader._impl.device())
+        self.buffer = symm.empty((self.world * self.job, self.dim), dtype=torch.float32, device=self.device)
+        self.handle = symm.rendezvous(self.buffer, self.group.group_name)
+        if not self.handle.multicast_ptr:
+            raise RuntimeError("symmetric memory without a multicast mapping (no NVLS on this box)")
+        self._flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+
+    def fill(self):
+        import torch
+
+        lo, hi = shard_range(self.rows, self.rank, self.world)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        slot = self.handle.multicast_ptr + self.rank * self.job * self.dim * 4
+        import torch.distributed as dist
+
+        dist.all_reduce(self._flag, group=self.group)  # nobody still reads the previous contents
+        self.reader._impl.decode_range_multicast(lo, hi, slot, stream)
+        dist.all_reduce(self._flag, group=self.group)  # every rank's kernel is complete: its rows have landed everywhere
+        return self.buffer[: self.rows]
+
+
 def _check_out(out, rows, dim, device):
     import torch
 
