@@ -740,7 +740,7 @@ def strong_scaling(args, ctx, reader, oracle):
             ctx["barrier"]()
             result["fused_decode_gather_ms"] = ctx["max_over_ranks"](timer.ms(fused.fill, reps=5, warm=2))
             result["fused_gb_per_s_into_each_gpu"] = rows * dim * 4 * (world - 1) / world / (result["fused_decode_gather_ms"] / 1e3) / 1e9
-            result["fused"] = "decode with multimem.st to torch symmetric memory's multicast address + one symmetric-memory barrier"
+            result["fused"] = "decode kernel storing to torch symmetric memory's NVLS multicast address (the switch replicates every store) + a one-element all-reduce as the barrier"
             fused_view = fused.fill()
             torch.cuda.synchronize()
             result["fused_available"] = True

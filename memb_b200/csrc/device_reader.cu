@@ -35,7 +35,7 @@ std::atomic<int64_t> g_optSymAverage{1};
 std::atomic<int64_t> g_optUniformRows{1};
 std::atomic<int64_t> g_optTrainedRows{1};   // trained_rows_kernel: 0 never, 1 unions of trained readers (one launch), 2 single lookups too
 std::atomic<int64_t> g_optRowsWarps{0};     // cap on resident warps of trained_rows_kernel (0 = as many as fit)
-std::atomic<int64_t> g_optTma{0};           // ring kernel bulk-async staging (EXPERIMENT, off: see DESIGN.md 4.4): 1 range decodes (one copy per tile), 2 also one copy per row
+std::atomic<int64_t> g_optTma{1};           // ring kernel bulk-async staging: 0 off, 1 range decodes (one copy per tile) and long records, 2 one copy per row everywhere
 std::atomic<int64_t> g_optFixedRecords{1};  // 0: keep the offset table even when fixed-stride records would be cheap  // dense uniform lookups: 0 element walk, 1 uniform_rows_kernel unless levels is a power of two, 2 always
 
 struct StatusError {

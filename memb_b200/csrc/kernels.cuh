@@ -618,21 +618,16 @@ __device__ __forceinline__ RowUnit ldsRowUnit(uint32_t addr)
     return v;
 }
 
-// The flush's store: streaming 128-bit store, or -- OutputSpec::multicast -- one multimem.st that the
-// NVSwitch replicates into every GPU of the multicast group (warp-uniform choice, no branch).
+// The flush's store.  An NVLS multicast address (OutputSpec::multicast: the NVSwitch replicates the
+// store into every GPU of the group) takes the same streaming store.  NOT multimem.st: ptxas 12.9
+// lowers a predicated `@p multimem.st.weak.global.v4.f32` to an UNPREDICATED STG.E.128 -- in the
+// first version every flush store ran twice and the predicated-off ones of the first / last chunk
+// clobbered the neighbouring rows (found r02 by a whole-matrix comparison); and a second, separately
+// predicated plain store beside the streaming one cost 2.5 % of the full-vocabulary decode.
 __device__ __forceinline__ void flushStoreF4If(uint32_t multicast, bool pred, void* ptr, float4 v)
 {
-    asm volatile(
-        "{\n"
-        ".reg .pred p, mc, uc;\n"
-        "setp.ne.u32 p, %5, 0;\n"
-        "setp.ne.and.u32 mc, %6, 0, p;\n"
-        "setp.eq.and.u32 uc, %6, 0, p;\n"
-        "@uc st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};\n"
-        "@mc multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};\n"
-        "}\n" ::"l"(ptr),
-        "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(static_cast<uint32_t>(pred)), "r"(multicast)
-        : "memory");
+    (void)multicast;
+    stcsF4If(pred, ptr, v);
 }
 
 // Four centroids for the four symbol fields packed in s4.  cb = shared address of
@@ -865,11 +860,8 @@ __device__ __forceinline__ uint32_t shflFrom(uint32_t v, uint32_t srcLane)
 // contiguous block of TrainedParams::blobTiled, already in the staged layout -- ONE bulk copy per
 // tile straight into a second staged-rows buffer, no copy-out, no row ids (4 bit: 0.576 vs 0.582 ms
 // for the 2.2 M-row table; 8 bit, 272 B records: 0.706 vs 0.775 ms).
-// BOTH MODES ARE OFF BY DEFAULT (option trained_tma): a whole-matrix comparison against the
-// register path shows the first 32 columns of the tile's FIRST row wrong in about 2 % of the
-// tiles a warp takes after its third -- timing dependent, not explained by the staged data or
-// the shared-memory layout (padding, a converged elect-predicated issue and an extra __syncwarp
-// after the wait change the rate, not the fact), and compute-sanitizer is closed on this pool.
+// Option trained_tma: 0 off, 1 (default) tiled range decodes + one copy per row for records longer
+// than the prefetch registers, 2 one copy per row everywhere.
 template <int G, bool VEC4, bool ESCAPE, bool SMALLCB, bool RMW, bool SIDE, int SYM, int TMA = 0>
 __global__ void __maxnreg__(TRAINED_MAX_REGS)
 trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, uint32_t rowBegin, uint64_t n,
