@@ -130,6 +130,24 @@ memb_b200_status memb_b200_decode_ids(memb_b200_reader* reader, const int32_t* i
                                       memb_b200_mem_kind ids_kind, uint64_t n, float* out,
                                       memb_b200_mem_kind out_kind, void* stream);
 
+/* Words -> rows WITHOUT ANY ALLOCATION.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same result as memb_b200_lookup_words / _on, but every
+ * buffer is the caller's and already on the reader's device: query text, n + 1 uint64 offsets, and the
+ * n x dim float output.  The one piece of scratch the lookup needs -- the n resolved row ids that
+ * resolve_words_kernel hands to the decode kernel -- lives in a file-scope `static __device__` array of
+ * MEMB_B200_NOALLOC_MAX_WORDS ids (4 MiB, held by every GPU that loads the library until exit)
+ * instead of the reader's cudaMalloc'ed, growing scratch.  n > MEMB_B200_NOALLOC_MAX_WORDS is rejected
+ * with MEMB_B200_ERR_ARGUMENT.  The call performs no cudaMalloc / cudaFree / stream-ordered allocation;
+ * both kernels are queued on `stream` and the call returns without waiting.
+ * The array is SHARED by every call in the process (all readers of a device): ids [0, n) are rewritten
+ * completely by each call and nothing in it has to start at zero, but two calls that overlap on the GPU
+ * (different streams, or different threads) race on it -- order them on one stream or with events. */
+#define MEMB_B200_NOALLOC_MAX_WORDS (1u << 20)
+memb_b200_status memb_b200_lookup_words_noalloc(memb_b200_reader* reader, const char* query_bytes_device,
+                                                const uint64_t* query_offsets_device, uint64_t n,
+                                                float* out_device, void* stream);
+
 /* Full-vocabulary path (Reader.tokenizer_embedding / to_keyed_vectors,
  * python/memb/reader.py:19-30,94-111): rows [row_begin, row_end) in row-id
  * order; a rank of a multi-GPU job passes its own slice. */

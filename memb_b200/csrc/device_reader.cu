@@ -152,6 +152,31 @@ T* deviceUpload(const T* host, size_t count, uint64_t& accounted)
     return d;
 }
 
+// ---- words -> rows without any allocation (memb_b200_lookup_words_noalloc) ----
+// The resolved row ids of one call.  In HOST code this name is only a stand-in for the symbol, never a
+// device address: the address is looked up once per device (with that device current) below.
+static __device__ __align__(256) int32_t g_noallocIds[MEMB_B200_NOALLOC_MAX_WORDS];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noallocMutex;
+int32_t* g_noallocIdsOnDevice[NOALLOC_MAX_DEVICES] = {};
+
+// Device address of g_noallocIds on `device`, which must be the CURRENT device.  Called at set-up
+// (memb_b200_open) and, should that have failed, again by the entry point.  Throws on a CUDA error.
+int32_t* noallocIdsFor(int device)
+{
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) {
+        fail(MEMB_B200_ERR_ARGUMENT, "lookup_words_noalloc: device ordinal out of range");
+    }
+    std::lock_guard<std::mutex> lock(g_noallocMutex);
+    if (!g_noallocIdsOnDevice[device]) {
+        void* ptr = nullptr;
+        CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_noallocIds));
+        g_noallocIdsOnDevice[device] = static_cast<int32_t*>(ptr);
+    }
+    return g_noallocIdsOnDevice[device];
+}
+
 }  // namespace
 
 struct memb_b200_reader {
@@ -1386,6 +1411,11 @@ memb_b200_status memb_b200_open(const char* path, int device, unsigned num_threa
         const auto t2 = std::chrono::steady_clock::now();
         CUDA_CHECK(cudaStreamSynchronize(reader->stream));
         reader->stats.prepare_ms += msSince(t2);
+        try {
+            noallocIdsFor(device);  // set-up of memb_b200_lookup_words_noalloc: symbol address, once per device
+        } catch (const StatusError&) {
+            cudaGetLastError();  // not fatal for open: the entry point retries and reports
+        }
         // the mmap is only needed for the vocabulary text of trained files
         if (reader->file->storage != STORAGE_TRAINED) {
             reader->file->map.reset();
@@ -1552,6 +1582,36 @@ memb_b200_status memb_b200_resolve_device(memb_b200_reader* reader, const char* 
         }
         DeviceGuard guard(reader->device);
         launchResolve(*reader, query_bytes_device, query_offsets_device, n, ids_device, static_cast<cudaStream_t>(stream));
+    });
+}
+
+memb_b200_status memb_b200_lookup_words_noalloc(memb_b200_reader* reader, const char* query_bytes_device,
+                                                const uint64_t* query_offsets_device, uint64_t n, float* out_device,
+                                                void* stream)
+{
+    return guarded([&] {
+        if (!reader) {
+            fail(MEMB_B200_ERR_ARGUMENT, "lookup_words_noalloc: null reader");
+        }
+        if (n > MEMB_B200_NOALLOC_MAX_WORDS) {
+            fail(MEMB_B200_ERR_ARGUMENT, "lookup_words_noalloc: " + std::to_string(n) + " words exceed the static scratch of " +
+                                             std::to_string(MEMB_B200_NOALLOC_MAX_WORDS) +
+                                             " (MEMB_B200_NOALLOC_MAX_WORDS); split the batch or use memb_b200_lookup_words_on");
+        }
+        if (n == 0) {
+            return;
+        }
+        if (!query_bytes_device || !query_offsets_device || !out_device) {
+            fail(MEMB_B200_ERR_ARGUMENT, "lookup_words_noalloc: null buffer");
+        }
+        memb_b200_reader& r = *reader;
+        DeviceGuard guard(r.device);
+        int32_t* dIds = noallocIdsFor(r.device);  // a device address, NOT the host-side name g_noallocIds
+        cudaStream_t s = static_cast<cudaStream_t>(stream);
+        launchResolve(r, query_bytes_device, query_offsets_device, n, dIds, s);
+        const uint32_t dim = r.file->dim;
+        K::OutputSpec o{out_device, dim, 0, 1.0f};
+        launchDecode(r, dIds, 0, n, o, K::EPI_WRITE, s);
     });
 }
 
