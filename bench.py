@@ -834,22 +834,33 @@ def sharded_union(args, ctx):
     missing = float(np.mean([np.all(p == 0, axis=1).mean() for p in parts]))
     for mode, cols in (("average", dim), ("concatenate", 2 * dim)):
         out = torch.empty((n, cols), dtype=torch.float32, device=device)
-        launches0 = _memb.launch_count()
+        want = np.mean(parts, axis=0) if mode == "average" else np.concatenate(parts, axis=-1)
 
         def device_step():
             for k, impl in enumerate(impls):
                 impl.resolve_into(d_blob.data_ptr(), d_offsets.data_ptr(), n, d_ids[k].data_ptr(), stream)
             _memb.union_decode_ids_into(impls, mode, d_ids.data_ptr(), True, n, out.data_ptr(), True, stream)
 
-        device_step()
-        launches_per_call = _memb.launch_count() - launches0
-        ctx["barrier"]()
-        ms = ctx["max_over_ranks"](timer.ms(device_step, reps=10))
-        decode_only = ctx["max_over_ranks"](timer.ms(
-            lambda: _memb.union_decode_ids_into(impls, mode, d_ids.data_ptr(), True, n, out.data_ptr(), True, stream), reps=10))
-        torch.cuda.synchronize()
-        want = np.mean(parts, axis=0) if mode == "average" else np.concatenate(parts, axis=-1)
-        ok = same_bits(want, out[:check].cpu().numpy())
+        def decode_step():
+            _memb.union_decode_ids_into(impls, mode, d_ids.data_ptr(), True, n, out.data_ptr(), True, stream)
+
+        def measure():
+            launches0 = _memb.launch_count()
+            device_step()
+            per_call = _memb.launch_count() - launches0
+            ctx["barrier"]()
+            both = ctx["max_over_ranks"](timer.ms(device_step, reps=10))
+            dec = ctx["max_over_ranks"](timer.ms(decode_step, reps=10))
+            torch.cuda.synchronize()
+            return both, dec, int(per_call), same_bits(want, out[:check].cpu().numpy())
+
+        # the fused ONE-launch kernel (trained_rows_kernel, option trained_rows_kernel = 1) beside the default
+        # (one ring-kernel launch per reader with fused merge epilogues): both measured, the faster is the default
+        _memb.set_option("trained_rows_kernel", 1)
+        one_ms, one_decode, one_launches, one_ok = measure()
+        _memb.set_option("trained_rows_kernel", 0)
+        ms, decode_only, launches_per_call, ok = measure()
+        ok = ok and one_ok
         # end to end: host blob -> device tensor through the words entry point (H2D + 2 x K0 + fused decode)
         packed = (blob, offsets)
         _memb.union_batch_embedding_into(impls, mode, packed, out.data_ptr(), n, True, stream)
@@ -867,7 +878,11 @@ def sharded_union(args, ctx):
                         "algorithmic_bytes_per_row_decode": bytes_row,
                         "roofline_frac_decode_per_gpu": n * bytes_row / (decode_only / 1e3) / 1e9 / peak,
                         "roofline_frac_resolve_and_decode_per_gpu": n * (bytes_row + bytes_row_k0) / (ms / 1e3) / 1e9 / peak,
-                        "words_api_host_blob_to_device_tensor_ms": e2e_ms, "out_columns": cols, "parity": ok}
+                        "words_api_host_blob_to_device_tensor_ms": e2e_ms, "out_columns": cols, "parity": ok,
+                        "one_launch_kernel": {"kernel": "trained_rows_kernel (option trained_rows_kernel=1)", "ms_decode": one_decode,
+                                              "ms_resolve_and_decode": one_ms, "decode_launches": one_launches - 2,
+                                              "roofline_frac_decode_per_gpu": n * bytes_row / (one_decode / 1e3) / 1e9 / peak,
+                                              "parity": one_ok}}
         result["parity"] = result["parity"] and ok
         del out
     result["parity"] = ctx["all_ranks_true"](result["parity"])

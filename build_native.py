@@ -45,7 +45,7 @@ def build_library(force=False):
     out = os.path.join(PKG, LIB_NAME)
     headers = [os.path.join(CSRC, name) for name in ("kernels.cuh", "trained_rows.cuh", "fb_format.h", "memb_file.h", "builder.h")]
     headers.append(os.path.join(INCLUDE, "memb_b200.h"))
-    sources = [os.path.join(CSRC, name) for name in ("device_reader.cu", "memb_file.cpp", "builder.cpp")]
+    sources = [os.path.join(CSRC, name) for name in ("device_reader.cu", "device_builder.cu", "memb_file.cpp", "builder.cpp")]
     if not force and not _newer(headers + sources, out):
         return out
     build_dir = os.path.join(PKG, "build")

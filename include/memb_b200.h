@@ -210,6 +210,12 @@ memb_b200_status memb_b200_builder_add_word(memb_b200_builder* builder, const ch
 /* Bulk form: n words as byte ranges of one blob, vectors as a row-major (n, dim) matrix. */
 memb_b200_status memb_b200_builder_add_words(memb_b200_builder* builder, const char* blob,
                                              const uint64_t* offsets, uint64_t n, const float* matrix);
+/* GPU converter (additive): run the bulk passes of the trained compressor --
+ * predict every value (src/kmeans.cpp:65-79), Huffman-encode every row byte-aligned
+ * (src/trained_compression.cpp:54-71) -- on CUDA device `device` at save(); -1 = host threads (default).
+ * The k-means fit on the 10 000-row sample stays on the host (its running mean is order dependent,
+ * src/kmeans.cpp:86-102).  The file is byte-identical either way. */
+memb_b200_status memb_b200_builder_set_device(memb_b200_builder* builder, int device);
 /* Builder::save — src/builder.cpp:64-68 */
 memb_b200_status memb_b200_builder_save(memb_b200_builder* builder, const char* path, unsigned num_threads);
 /* availableCompressionStrategies() — src/compression_strategy.cpp:63-78; returns "full\0uniform\0trained\0\0" */

@@ -40,10 +40,10 @@ def read_vectors(filename, max_words=None, out=sys.stdout):
     return kept, dim
 
 
-def convert(source_filename, dest_filename, quantization, bits_per_weight=4, max_words=None, out=sys.stdout):
+def convert(source_filename, dest_filename, quantization, bits_per_weight=4, max_words=None, out=sys.stdout, device=None):
     """Returns the number of words written."""
     vectors, dim = read_vectors(source_filename, max_words, out)
-    builder = Builder(dim, quantization, bits_per_weight)
+    builder = Builder(dim, quantization, bits_per_weight, device=device)
     written = 0
     for word, vector in vectors:
         try:
@@ -66,12 +66,15 @@ def parse_args(argv=None):
                         help='Bits per weight; a value outside the range of the strategy is clamped to it')
     parser.add_argument('--max-words', dest='max_words', type=int,
                         help='Convert at most this many lines (default: all)')
+    parser.add_argument('--device', dest='device', type=int, default=None,
+                        help='(additive) CUDA ordinal: encode the "trained" storage on that GPU; the file is the same')
     return parser.parse_args(argv)
 
 
 def main(argv=None):
     args = parse_args(argv)
-    convert(args.source_filename, args.dest_filename, args.quantization, args.bits_per_weight, args.max_words)
+    convert(args.source_filename, args.dest_filename, args.quantization, args.bits_per_weight, args.max_words,
+            device=args.device)
     return 0
 
 

@@ -696,6 +696,7 @@ public:
     }
 
     void setDim(size_t dim) { dim_ = dim; }
+    void setDevice(int device) { check(memb_b200_builder_set_device(impl_, device)); }
 
 private:
     memb_b200_builder* impl_ = nullptr;
@@ -718,11 +719,16 @@ PYBIND11_MODULE(_memb, m)
     m.doc() = "memb_b200: B200-native drop-in for memb's _memb extension module";
 
     py::class_<Builder>(m, "Builder")
-        .def(py::init([](size_t dim, const std::string& storage, size_t bits) {
-            auto b = std::make_unique<Builder>(dim, storage, bits);
-            b->setDim(dim);
-            return b;
-        }))
+        .def(py::init([](size_t dim, const std::string& storage, size_t bits, int device) {
+                 auto b = std::make_unique<Builder>(dim, storage, bits);
+                 b->setDim(dim);
+                 if (device >= 0) {
+                     b->setDevice(device);
+                 }
+                 return b;
+             }),
+             py::arg("dim"), py::arg("storage_name"), py::arg("bits_per_weight"), py::arg("device") = -1)
+        .def("set_device", &Builder::setDevice, py::arg("device"))
         .def("add_word", &Builder::addWord)
         .def("save", [](Builder& b, const std::string& filename) { b.save(filename, 0); })
         // additive

@@ -290,6 +290,94 @@ IndexHeader writeIndex(fb::Writer& w, uint8_t storageType, uint32_t dim)
 
 }  // namespace
 
+// The bulk passes of the trained compressor on the host threads (src/trained_compression.cpp:54-71);
+// device_builder.cu holds the GPU version, which must stay byte-identical to this one.
+TrainedEncoding encodeTrainedOnHost(const float* values, size_t n, size_t dim, const KMeans1D& km, unsigned threads)
+{
+    // quantise every row; remember the order in which symbols first appear
+    std::vector<uint8_t> symbols(n * dim);
+    std::vector<std::vector<size_t>> partCounts(threads, std::vector<size_t>(256, 0));
+    std::vector<std::vector<uint64_t>> partFirst(threads, std::vector<uint64_t>(256, ~0ull));
+    parallelRows(n, threads, [&](unsigned t, size_t b, size_t e) {
+        auto& counts = partCounts[t];
+        auto& first = partFirst[t];
+        for (size_t i = b * dim; i < e * dim; ++i) {
+            const uint8_t s = km.predictOne(values[i]);
+            symbols[i] = s;
+            if (counts[s]++ == 0) {
+                first[s] = i;
+            }
+        }
+    });
+    std::vector<size_t> counts(256, 0);
+    std::vector<uint64_t> first(256, ~0ull);
+    for (unsigned t = 0; t < threads; ++t) {
+        for (int s = 0; s < 256; ++s) {
+            counts[s] += partCounts[t][s];
+            first[s] = std::min(first[s], partFirst[t][s]);
+        }
+    }
+    std::vector<std::pair<uint64_t, uint8_t>> seenOrder;
+    for (int s = 0; s < 256; ++s) {
+        if (counts[s]) {
+            seenOrder.push_back({first[s], static_cast<uint8_t>(s)});
+        }
+    }
+    std::sort(seenOrder.begin(), seenOrder.end());
+    std::vector<std::pair<uint8_t, size_t>> firstSeen;
+    for (const auto& p : seenOrder) {
+        firstSeen.push_back({p.second, counts[p.second]});
+    }
+    if (firstSeen.empty()) {
+        throw std::runtime_error("Cannot save an empty trained index");
+    }
+    TrainedEncoding enc;
+    enc.code = buildHuffmanCode(firstSeen);
+    const HuffmanCode& hc = enc.code;
+
+    // every row is its own byte-aligned, zero-padded, MSB-first bit stream,
+    // appended in insertion order (src/trained_compression.cpp:65-71)
+    std::vector<uint64_t>& rowStart = enc.rowStart;
+    rowStart.assign(n + 1, 0);
+    parallelRows(n, threads, [&](unsigned, size_t b, size_t e) {
+        for (size_t r = b; r < e; ++r) {
+            uint64_t bitsTotal = 0;
+            for (size_t i = 0; i < dim; ++i) {
+                bitsTotal += hc.lengthOf[symbols[r * dim + i]];
+            }
+            rowStart[r + 1] = (bitsTotal + 7) / 8;
+        }
+    });
+    for (size_t r = 0; r < n; ++r) {
+        rowStart[r + 1] += rowStart[r];
+    }
+    if (rowStart[n] > 0xffffffffULL) {
+        throw std::runtime_error("packed_values exceeds the 32-bit offsets of the format");
+    }
+    std::vector<uint8_t>& packed = enc.packed;
+    packed.assign(rowStart[n], 0);
+    parallelRows(n, threads, [&](unsigned, size_t b, size_t e) {
+        for (size_t r = b; r < e; ++r) {
+            uint8_t* dst = packed.data() + rowStart[r];
+            uint64_t acc = 0;
+            unsigned have = 0;
+            for (size_t i = 0; i < dim; ++i) {
+                const uint8_t s = symbols[r * dim + i];
+                acc = (acc << hc.lengthOf[s]) | hc.codeOf[s];
+                have += hc.lengthOf[s];
+                while (have >= 8) {
+                    *dst++ = static_cast<uint8_t>(acc >> (have - 8));
+                    have -= 8;
+                }
+            }
+            if (have) {
+                *dst++ = static_cast<uint8_t>(acc << (8 - have));
+            }
+        }
+    });
+    return enc;
+}
+
 std::vector<uint8_t> Builder::serialize(unsigned numThreads)
 {
     namespace I = fb::ids;
@@ -306,83 +394,11 @@ std::vector<uint8_t> Builder::serialize(unsigned numThreads)
         const size_t sampleRows = std::min(CLUSTER_SAMPLE_ROWS, n);
         km.fit(values_.data(), sampleRows * dim, levels);
 
-        // quantise every row; remember the order in which symbols first appear
-        std::vector<uint8_t> symbols(n * dim);
-        std::vector<std::vector<size_t>> partCounts(threads, std::vector<size_t>(256, 0));
-        std::vector<std::vector<uint64_t>> partFirst(threads, std::vector<uint64_t>(256, ~0ull));
-        parallelRows(n, threads, [&](unsigned t, size_t b, size_t e) {
-            auto& counts = partCounts[t];
-            auto& first = partFirst[t];
-            for (size_t i = b * dim; i < e * dim; ++i) {
-                const uint8_t s = km.predictOne(values_[i]);
-                symbols[i] = s;
-                if (counts[s]++ == 0) {
-                    first[s] = i;
-                }
-            }
-        });
-        std::vector<size_t> counts(256, 0);
-        std::vector<uint64_t> first(256, ~0ull);
-        for (unsigned t = 0; t < threads; ++t) {
-            for (int s = 0; s < 256; ++s) {
-                counts[s] += partCounts[t][s];
-                first[s] = std::min(first[s], partFirst[t][s]);
-            }
-        }
-        std::vector<std::pair<uint64_t, uint8_t>> seenOrder;
-        for (int s = 0; s < 256; ++s) {
-            if (counts[s]) {
-                seenOrder.push_back({first[s], static_cast<uint8_t>(s)});
-            }
-        }
-        std::sort(seenOrder.begin(), seenOrder.end());
-        std::vector<std::pair<uint8_t, size_t>> firstSeen;
-        for (const auto& p : seenOrder) {
-            firstSeen.push_back({p.second, counts[p.second]});
-        }
-        if (firstSeen.empty()) {
-            throw std::runtime_error("Cannot save an empty trained index");
-        }
-        const HuffmanCode hc = buildHuffmanCode(firstSeen);
-
-        // every row is its own byte-aligned, zero-padded, MSB-first bit stream,
-        // appended in insertion order (src/trained_compression.cpp:65-71)
-        std::vector<uint64_t> rowStart(n + 1, 0);
-        parallelRows(n, threads, [&](unsigned, size_t b, size_t e) {
-            for (size_t r = b; r < e; ++r) {
-                uint64_t bitsTotal = 0;
-                for (size_t i = 0; i < dim; ++i) {
-                    bitsTotal += hc.lengthOf[symbols[r * dim + i]];
-                }
-                rowStart[r + 1] = (bitsTotal + 7) / 8;
-            }
-        });
-        for (size_t r = 0; r < n; ++r) {
-            rowStart[r + 1] += rowStart[r];
-        }
-        if (rowStart[n] > 0xffffffffULL) {
-            throw std::runtime_error("packed_values exceeds the 32-bit offsets of the format");
-        }
-        std::vector<uint8_t> packed(rowStart[n], 0);
-        parallelRows(n, threads, [&](unsigned, size_t b, size_t e) {
-            for (size_t r = b; r < e; ++r) {
-                uint8_t* dst = packed.data() + rowStart[r];
-                uint64_t acc = 0;
-                unsigned have = 0;
-                for (size_t i = 0; i < dim; ++i) {
-                    const uint8_t s = symbols[r * dim + i];
-                    acc = (acc << hc.lengthOf[s]) | hc.codeOf[s];
-                    have += hc.lengthOf[s];
-                    while (have >= 8) {
-                        *dst++ = static_cast<uint8_t>(acc >> (have - 8));
-                        have -= 8;
-                    }
-                }
-                if (have) {
-                    *dst++ = static_cast<uint8_t>(acc << (8 - have));
-                }
-            }
-        });
+        const TrainedEncoding enc = device_ >= 0 ? encodeTrainedOnDevice(device_, values_.data(), n, dim, km)
+                                                  : encodeTrainedOnHost(values_.data(), n, dim, km, threads);
+        const HuffmanCode& hc = enc.code;
+        const std::vector<uint64_t>& rowStart = enc.rowStart;
+        const std::vector<uint8_t>& packed = enc.packed;
 
         std::string packedWords;
         std::vector<uint32_t> wordOffsets(n), valueOffsets(n);

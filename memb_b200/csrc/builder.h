@@ -39,6 +39,11 @@ public:
     std::vector<uint8_t> serialize(unsigned numThreads = 0);
     void save(const std::string& filename, unsigned numThreads = 0);
 
+    // Additive: run the bulk passes of the trained compressor (predict, row sizes,
+    // bit packing) on CUDA device `device` instead of the host threads; -1 = host.  The file is
+    // byte-identical either way.  Other storages ignore it.
+    void setDevice(int device) { device_ = device; }
+
     size_t dim() const { return dim_; }
     size_t size() const { return words_.size(); }
 
@@ -49,6 +54,7 @@ private:
     std::vector<std::string> words_;
     std::vector<float> values_;  // row-major, insertion order
     std::unordered_set<std::string> seen_;
+    int device_ = -1;
 };
 
 const std::vector<std::string>& availableCompressionStrategies();
@@ -73,5 +79,18 @@ struct HuffmanCode {
 // counts in first-occurrence order of the symbols (this is what fixes the
 // tie-breaks of the reference's unordered_map-driven construction).
 HuffmanCode buildHuffmanCode(const std::vector<std::pair<uint8_t, size_t>>& countsInFirstSeenOrder);
+
+// Everything of a trained file that depends on ALL values: the prefix code, where every row (in
+// insertion order) starts in packed_values, and packed_values itself
+// (src/trained_compression.cpp:54-71).
+struct TrainedEncoding {
+    HuffmanCode code;
+    std::vector<uint64_t> rowStart;  // n + 1 byte offsets
+    std::vector<uint8_t> packed;
+};
+TrainedEncoding encodeTrainedOnHost(const float* values, size_t n, size_t dim, const KMeans1D& km, unsigned threads);
+// device_builder.cu (nvcc): the same on a GPU, byte-identical; throws runtime_error on CUDA errors
+TrainedEncoding encodeTrainedOnDevice(int device, const float* values, size_t n, size_t dim, const KMeans1D& km);
+int deviceEncoderCount();
 
 }  // namespace memb_b200

@@ -33,7 +33,7 @@ std::atomic<int64_t> g_optGeneric{0};
 std::atomic<int64_t> g_optPassRows{0};
 std::atomic<int64_t> g_optSymAverage{1};
 std::atomic<int64_t> g_optUniformRows{1};
-std::atomic<int64_t> g_optTrainedRows{1};   // trained_rows_kernel: 0 never, 1 unions of trained readers (one launch), 2 single lookups too
+std::atomic<int64_t> g_optTrainedRows{0};   // trained_rows_kernel: 0 never (default: measured slower than the ring kernel), 1 unions of trained readers in ONE launch, 2 single lookups too
 std::atomic<int64_t> g_optRowsWarps{0};     // cap on resident warps of trained_rows_kernel (0 = as many as fit)
 std::atomic<int64_t> g_optTma{1};           // ring kernel bulk-async staging: 0 off, 1 range decodes (one copy per tile) and long records, 2 one copy per row everywhere
 std::atomic<int64_t> g_optFixedRecords{1};  // 0: keep the offset table even when fixed-stride records would be cheap  // dense uniform lookups: 0 element walk, 1 uniform_rows_kernel unless levels is a power of two, 2 always
@@ -1905,6 +1905,20 @@ memb_b200_status memb_b200_builder_add_words(memb_b200_builder* builder, const c
         } catch (const std::runtime_error& e) {
             fail(MEMB_B200_ERR_BUILDER, e.what());
         }
+    });
+}
+
+memb_b200_status memb_b200_builder_set_device(memb_b200_builder* builder, int device)
+{
+    return guarded([&] {
+        if (!builder) {
+            fail(MEMB_B200_ERR_ARGUMENT, "builder_set_device: null builder");
+        }
+        if (device < -1 || device >= deviceEncoderCount()) {
+            fail(device >= 0 && deviceEncoderCount() == 0 ? MEMB_B200_ERR_NO_DEVICE : MEMB_B200_ERR_ARGUMENT,
+                 "builder_set_device: no CUDA device " + std::to_string(device));
+        }
+        builder->impl.setDevice(device);
     });
 }
 

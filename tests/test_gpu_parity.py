@@ -182,7 +182,7 @@ def test_trained_kernel_variants(abi, oracle, synthetic, bits):
             reader.close()
             second.close()
     finally:
-        abi.lib.memb_b200_set_option(b"trained_rows_kernel", 1)
+        abi.lib.memb_b200_set_option(b"trained_rows_kernel", 0)
         abi.lib.memb_b200_set_option(b"trained_fixed_records", 1)
 
 
@@ -517,6 +517,35 @@ def test_device_results_are_ordered_on_the_callers_stream(oracle, synthetic):
             assert bits_equal(got.cpu().numpy(), expect)
 
 
+# ---- GPU converter ----
+@pytest.mark.parametrize("bits,rows,dim", [(1, 2000, 300), (2, 2000, 300), (3, 1500, 64), (4, 12000, 300), (5, 2000, 301),
+                                           (6, 3000, 100), (7, 2000, 300), (8, 11000, 300), (4, 1, 1), (8, 40, 3)])
+def test_gpu_converter_matches_cpu_builder(oracle, workdir, bits, rows, dim):
+    """Builder(..., device=0) runs predict / row sizes / bit packing on the GPU (device_builder.cu); the file
+    must be BYTE-identical to the host encoder's -- same symbols, same first-occurrence order (Huffman
+    tie-breaks), same packed rows -- and decode to the same rows.  More than 10 000 rows: values beyond the
+    k-means sample; NaN / inf / huge values: the lower_bound's comparison semantics."""
+    import memb_b200
+
+    rng = np.random.default_rng(1000 * bits + dim)
+    matrix = rng.standard_normal((rows, dim), dtype=np.float32)
+    if rows > 100:
+        matrix[rows // 2, 0] = np.nan
+        matrix[rows // 2, 1 % dim] = np.inf
+        matrix[rows // 3, 0] = -3e38
+    words = ["g%x" % i for i in rng.permutation(rows)]
+    paths = {}
+    for name, device in (("cpu", None), ("gpu", 0)):
+        builder = memb_b200.Builder(dim, "trained", bits, device=device)
+        builder.add_words(words, matrix)
+        paths[name] = str(workdir / ("conv_%s_%d_%d_%d.bin" % (name, bits, rows, dim)))
+        builder.save(paths[name])
+    cpu, gpu = open(paths["cpu"], "rb").read(), open(paths["gpu"], "rb").read()
+    assert cpu == gpu
+    reader = memb_b200.Reader(paths["gpu"])
+    assert bits_equal(reader.decode_range(0, rows), oracle.open(paths["cpu"]).decode_range(0, rows))
+
+
 # ---- additive word-collection forms and device-resident results (SURVEY 8(f)-2/3) ----
 def test_word_collection_forms_and_device_tensors(oracle, synthetic):
     import torch
@@ -710,14 +739,16 @@ def test_union_average_through_symbol_words(abi, oracle, synthetic, bits0, bits1
     parts = [o.batch_embedding(words) for o in oracles]
     for count in (2, 3):
         want = np.mean(parts[:count], axis=0)
-        # default: two trained readers = ONE launch of trained_rows_kernel
+        # default: the multi-launch ring path -- symbol words for the first two readers
         assert bits_equal(helpers.union_lookup_words(abi, readers[:count], abi.AVERAGE, words, dim), want)
         try:
-            # the multi-launch ring path: symbol words, then plain read-modify-write
-            abi.check(abi.lib.memb_b200_set_option(b"trained_rows_kernel", 0))
+            # two trained readers in ONE launch of trained_rows_kernel (three: falls back to the ring path)
+            abi.check(abi.lib.memb_b200_set_option(b"trained_rows_kernel", 1))
             assert bits_equal(helpers.union_lookup_words(abi, readers[:count], abi.AVERAGE, words, dim), want)
+            abi.check(abi.lib.memb_b200_set_option(b"trained_rows_kernel", 0))
+            # plain read-modify-write of the output
             abi.check(abi.lib.memb_b200_set_option(b"union_symbol_average", 0))
             assert bits_equal(helpers.union_lookup_words(abi, readers[:count], abi.AVERAGE, words, dim), want)
         finally:
             abi.lib.memb_b200_set_option(b"union_symbol_average", 1)
-            abi.lib.memb_b200_set_option(b"trained_rows_kernel", 1)
+            abi.lib.memb_b200_set_option(b"trained_rows_kernel", 0)

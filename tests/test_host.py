@@ -68,6 +68,18 @@ def test_truncated_files_are_rejected_not_crashing(abi, synthetic, workdir):
             assert not handle
 
 
+def test_gpu_converter_needs_a_device(abi):
+    """Builder(device=...) never falls back to the host silently."""
+    import memb_b200
+
+    if abi.lib.memb_b200_device_count() == 0:
+        with pytest.raises((RuntimeError, ValueError)):
+            memb_b200.Builder(3, "trained", 4, device=0)
+    with pytest.raises((RuntimeError, ValueError)):
+        memb_b200.Builder(3, "trained", 4, device=4096)
+    memb_b200.Builder(3, "trained", 4, device=None)  # host encoder
+
+
 def test_builder_errors():
     import memb_b200
 
