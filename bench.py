@@ -956,6 +956,32 @@ def extras(args, ctx, reader):
                                             "note": "latency-bound random probes (slot 8 B, then the key text); not a bandwidth kernel"}
     del d_blob, d_offsets, d_ids, words, packed
 
+    # ---- the write path: Builder.save of a trained 4-bit table, host threads vs GPU converter ----
+    conv_rows = min(args.rows, 500_000)
+    rng = np.random.Generator(np.random.PCG64(90))
+    matrix = rng.standard_normal((conv_rows, dim), dtype=np.float32)
+    conv_words = ["k%x" % i for i in rng.permutation(conv_rows)]
+    conv = {}
+    for name, dev in (("host_threads", None), ("gpu", device.index)):
+        builder = memb_b200.Builder(dim, "trained", args.bits, device=dev)
+        builder.add_words(conv_words, matrix)
+        path = os.path.join(args.cache_dir, "converter_probe_%s.bin" % name)
+        t0 = time.perf_counter()
+        builder.save(path)
+        conv[name] = {"save_s": time.perf_counter() - t0, "path": path}
+        del builder
+    with open(conv["host_threads"]["path"], "rb") as fa, open(conv["gpu"]["path"], "rb") as fb:
+        same_file = fa.read() == fb.read()
+    for entry in conv.values():
+        os.remove(entry.pop("path"))
+    result["gpu_converter"] = {"rows": conv_rows, "dim": dim, "bits": args.bits, "host_threads_save_s": conv["host_threads"]["save_s"],
+                               "gpu_save_s": conv["gpu"]["save_s"], "files_byte_identical": same_file,
+                               "host_cpus": os.cpu_count(),
+                               "note": "save() = k-means fit on the 10 000-row sample (host, sequential in both) + predict / "
+                                       "Huffman-encode all rows (host threads or GPU, incl. the 0.6 GB H2D from pageable memory) "
+                                       "+ word sort + file write"}
+    del matrix, conv_words
+
     # ---- configs[0]: 10 k x dim, trained 6 bit through the converter; 1 k words incl. 5 % misses ----
     c1_path = build_c1_table(args)
     small = memb_b200.Reader(c1_path, device=device.index)

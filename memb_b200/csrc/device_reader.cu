@@ -32,6 +32,7 @@ std::atomic<int64_t> g_optWarps{0};
 std::atomic<int64_t> g_optGeneric{0};
 std::atomic<int64_t> g_optPassRows{0};
 std::atomic<int64_t> g_optSymAverage{1};
+std::atomic<int64_t> g_optPairTable{1};     // average through symbol words: merged values from a pair table when the codebooks are small
 std::atomic<int64_t> g_optUniformRows{1};
 std::atomic<int64_t> g_optTrainedRows{0};   // trained_rows_kernel: 0 never (default: measured slower than the ring kernel), 1 unions of trained readers in ONE launch, 2 single lookups too
 std::atomic<int64_t> g_optRowsWarps{0};     // cap on resident warps of trained_rows_kernel (0 = as many as fit)
@@ -730,7 +731,8 @@ void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t
     const K::TrainedParams& p = r.trained;
     const K::TrainedLayout lay = K::trainedLayout(
         r.smemBase, K::trainedLutBytes(p.lutBits, p.lutReplicas),
-        K::trainedWarpBytes(p.rowWords, TMA ? K::trainedLandingBytes(p.recUnits) : 0u), r.trainedWarps, p.lut2Entries);
+        K::trainedWarpBytes(p.rowWords, TMA ? K::trainedLandingBytes(p.recUnits) : 0u), r.trainedWarps,
+        SYM == 2 ? o.pairEntries : p.lut2Entries);
     const size_t smemBytes = lay.end - r.smemBase;
     const uint64_t tiles = (n + 31) / 32;
     const unsigned grid = static_cast<unsigned>(
@@ -1226,6 +1228,23 @@ void launchUnion(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_m
         specs[1].symCodebook = readers[0]->trained.codebook;
         specs[1].symCodebookSize = readers[0]->trained.codebookSize;
         specs[1].symFieldShift = 2u - readers[0]->trained.symShift;
+        // small codebooks: T[s0][s1] for every symbol pair (+0.0 slots of missing words included) instead of
+        // two gathers + add + scale per element -- when the table fits beside this reader's warps
+        const memb_b200_reader& r1 = *readers[1];
+        uint32_t log2Stride = 0;
+        while ((1u << log2Stride) < r1.trained.codebookSize + 1) {
+            ++log2Stride;
+        }
+        const uint32_t entries = (readers[0]->trained.codebookSize + 1) << log2Stride;
+        if (g_optPairTable.load() && entries <= 4096) {
+            const K::TrainedLayout lay = K::trainedLayout(
+                r1.smemBase, K::trainedLutBytes(r1.trained.lutBits, r1.trained.lutReplicas),
+                K::trainedWarpBytes(r1.trained.rowWords, 0u), r1.trainedWarps, entries);
+            if (lay.end - r1.smemBase <= r1.smemOptin) {
+                specs[1].pairEntries = entries;
+                specs[1].pairLog2 = log2Stride;
+            }
+        }
     }
     for (uint32_t k = 0; k < R; ++k) {
         int epi = K::EPI_WRITE;
@@ -1313,6 +1332,8 @@ memb_b200_status memb_b200_set_option(const char* name, int64_t value)
             g_optGeneric = value;
         } else if (key == "union_symbol_average" && (value == 0 || value == 1)) {
             g_optSymAverage = value;
+        } else if (key == "union_pair_table" && (value == 0 || value == 1)) {
+            g_optPairTable = value;
         } else if (key == "uniform_rows_kernel" && value >= 0 && value <= 2) {
             g_optUniformRows = value;
         } else if (key == "trained_rows_kernel" && value >= 0 && value <= 2) {
@@ -1377,14 +1398,16 @@ memb_b200_status memb_b200_open(const char* path, int device, unsigned num_threa
         reader->smemOptin = static_cast<size_t>(value);
         CUDA_CHECK(cudaStreamCreateWithFlags(&reader->stream, cudaStreamNonBlocking));
         {
-            // stream-ordered scratch of the union stitch pass (launchUnion): let the device's
-            // default pool keep up to 256 MiB instead of returning it at every synchronisation
+            // stream-ordered scratch of launchUnion (symbol words of an average: dim bytes per row, 1.2 GB for
+            // 4 M rows; side buffers of a concatenate): let the device's default pool KEEP what it has reserved
+            // instead of returning it at every synchronisation.  With the 256 MiB of round 1 a 1 M-row average
+            // (300 MB) paid a real device allocation after every sync: 0.76 -> up to 1.0 ms per call (r02).
             cudaMemPool_t pool = nullptr;
             if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
                 uint64_t threshold = 0;
                 cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
-                if (threshold < (uint64_t(256) << 20)) {
-                    threshold = uint64_t(256) << 20;
+                if (threshold < (uint64_t(8) << 30)) {
+                    threshold = uint64_t(8) << 30;
                     cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
                 }
             }

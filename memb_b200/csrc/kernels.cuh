@@ -67,6 +67,12 @@ struct OutputSpec {
     const float* symCodebook = nullptr;  // reader 0's centroids (SYM == 2)
     uint32_t symCodebookSize = 0;
     uint32_t symFieldShift = 0;          // reader 0's symbol field -> byte offset into its codebook
+    // SYM == 2 with small codebooks: the merged value depends on the symbol PAIR only, so the launch
+    // builds T[s0][s1] = epilogue(c0[s0], c1[s1]) once per CTA ((size0 + 1) x pairStride entries, the
+    // +0.0 slots of missing words included) and the flush gathers ONE value per element instead of two
+    // centroids + add + scale.  Same device arithmetic as the two-gather flush: bit-identical.
+    uint32_t pairEntries = 0;            // 0: two-gather flush
+    uint32_t pairLog2 = 0;               // log2 of the table's row stride (>= size1 + 1)
 };
 
 // Where the 16 B unit `unit` of output row i goes (see OutputSpec::sideHead).
@@ -661,6 +667,17 @@ __device__ __forceinline__ float4 gatherCentroidsShift(uint32_t cb, uint32_t s4,
     v.w = ldsF32(cb + ((s4 >> 24) << shift));
     return v;
 }
+// Four merged values for four symbol pairs: f0 / f1 = packed symbol fields of reader 0 / reader 1,
+// sh0 / sh1 turn a field into its byte offset contribution (OutputSpec::pairEntries).
+__device__ __forceinline__ float4 gatherPairs(uint32_t pairBase, uint32_t f0, uint32_t f1, uint32_t sh0, uint32_t sh1)
+{
+    float4 v;
+    v.x = ldsF32(pairBase + ((f0 & 0xffu) << sh0) + ((f1 & 0xffu) << sh1));
+    v.y = ldsF32(pairBase + (((f0 >> 8) & 0xffu) << sh0) + (((f1 >> 8) & 0xffu) << sh1));
+    v.z = ldsF32(pairBase + (((f0 >> 16) & 0xffu) << sh0) + (((f1 >> 16) & 0xffu) << sh1));
+    v.w = ldsF32(pairBase + ((f0 >> 24) << sh0) + ((f1 >> 24) << sh1));
+    return v;
+}
 __device__ __forceinline__ uint32_t ldU32If(bool pred, const uint32_t* ptr)
 {
     uint32_t v = 0;
@@ -875,7 +892,8 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     const uint32_t lutBytes = trainedLutBytes(p.lutBits, p.lutReplicas);
     const uint32_t base = smemAddr(smem);
     const uint32_t perWarp = trainedWarpBytes(p.rowWords, TMA ? trainedLandingBytes(p.recUnits) : 0u);
-    const TrainedLayout lay = trainedLayout(base, lutBytes, perWarp, warpsPerCta, p.lut2Entries);
+    // (the region behind the codebooks holds the second-level table, or -- SYM == 2, never with long codes -- the pair table)
+    const TrainedLayout lay = trainedLayout(base, lutBytes, perWarp, warpsPerCta, SYM == 2 ? o.pairEntries : p.lut2Entries);
     {
         uint32_t dynBytes;
         asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dynBytes));
@@ -912,6 +930,15 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                         }
                     }
                 }
+            }
+        }
+        if (SYM == 2) {
+            float* pairS = reinterpret_cast<float*>(smem + (lay.lut2 - base));
+            for (uint32_t i = threadIdx.x; i < o.pairEntries; i += blockDim.x) {
+                const uint32_t s0 = i >> o.pairLog2, s1 = i & ((1u << o.pairLog2) - 1u);
+                const float c0 = s0 < o.symCodebookSize ? o.symCodebook[s0] : 0.f;
+                const float c1 = s1 < p.codebookSize ? p.codebook[s1] : 0.f;
+                pairS[i] = applyEpilogue(c1, c0, epi, o.divisor);  // c0 + c1 in reader order, / R for the last reader
             }
         }
         if (ESCAPE) {
@@ -1190,16 +1217,27 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         for (uint32_t c0 = 0; c0 < dim; c0 += TRAINED_CHUNK) {
             const uint32_t nsym = min(TRAINED_CHUNK, dim - c0);
             const uint32_t word0 = (c0 / 4) & (TRAINED_RING_UNITS - 1);  // ring position of this chunk's first word
+            // SYM == 2: the symbol words this chunk's flush adds to are LOADED here, before the decode, and
+            // consumed after it (eight registers per lane; fp32 running sums would be 32: L2 prefetch only).
+            // Measured r02 on the two-reader average, 1 M Zipf words: 0.787 ms two-gather flush -> 0.764 with
+            // the pair table -> 0.762 with these loads ahead.  The launch's cost is its flush's INSTRUCTIONS
+            // (ncu: 226 M warp instructions against 119 M for a plain decode; 43 M bank conflicts on the pair
+            // table, which spans every bank, against none on a 16-entry codebook) -- yet a predicate-free
+            // straight-line flush for middle chunks, as the plain path has, was SLOWER (0.83-0.91 ms): its
+            // burst of 32 gathers + 8 stores per lane queues in front of the other warps' LUT loads.
+            uint32_t symAhead[TRAINED_CHUNK_UNITS];
             if (RMW && fastFlush) {
                 // the flush of this chunk will read these 16 B units of the running sum
                 const int ub = int(c0 / 4);
                 const int ua = int((c0 + nsym) / 4);
+                const bool lastChunk = c0 + TRAINED_CHUNK >= dim;
 #pragma unroll
                 for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
                     const int a = int((aBase + it * aStep) & 7u);
                     const int j = ub - a + int(fq);
                     if (SYM == 2) {
-                        prefetchL2If(j >= 0 && j < ua, symRow0 + it * symStep + j);
+                        // (exactly the predicate of the flush's first pass)
+                        symAhead[it] = ldU32If(j >= 0 && j < (lastChunk ? ua : ua - a), symRow0 + it * symStep + j);
                     } else {
                         prefetchL2If(j >= 0 && j < ua, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j);
                     }
@@ -1265,7 +1303,8 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int j = unitsBefore - a + int(fq) + shift;
                             const int end = last ? end0 : unitsAfter - a;
                             if (SYM == 2) {
-                                old[it].x = __uint_as_float(ldU32If(j >= 0 && j < end, symRow0 + it * symStep + j));
+                                old[it].x = __uint_as_float(pass == 0 ? symAhead[it]
+                                                                      : ldU32If(j >= 0 && j < end, symRow0 + it * symStep + j));
                             } else {
                                 old[it] = ldF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j);
                             }
@@ -1276,9 +1315,15 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int j = unitsBefore - a + int(fq) + shift;
                             const int end = last ? end0 : unitsAfter - a;
                             const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
-                            const float4 sum = SYM == 2 ? gatherCentroidsShift(cb0, __float_as_uint(old[it].x), o.symFieldShift)
-                                                        : old[it];
-                            const float4 v = applyEpilogue4(gatherCentroids<SMALLCB>(cb, s4), sum, epi, o.divisor);
+                            float4 v;
+                            if (SYM == 2 && o.pairEntries) {
+                                v = gatherPairs(lay.lut2, __float_as_uint(old[it].x), s4, o.pairLog2 + o.symFieldShift,
+                                                SMALLCB ? 0u : 2u);
+                            } else {
+                                const float4 sum = SYM == 2 ? gatherCentroidsShift(cb0, __float_as_uint(old[it].x), o.symFieldShift)
+                                                            : old[it];
+                                v = applyEpilogue4(gatherCentroids<SMALLCB>(cb, s4), sum, epi, o.divisor);
+                            }
                             stcsF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j, v);
                         }
                     }
