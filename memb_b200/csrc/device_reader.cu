@@ -219,7 +219,8 @@ struct memb_b200_reader {
 
     Scratch scratchIds, scratchOut, scratchQuery, scratchOffsets;
     // dynamic tile scheduling of the trained kernel: one counter per launch in flight
-    static constexpr uint32_t TILE_COUNTERS = 256;
+    // (a ring: a slot is reused after TILE_COUNTERS launches -- far more than can be in flight on a device)
+    static constexpr uint32_t TILE_COUNTERS = 4096;
     uint32_t* dTileCounters = nullptr;
     std::atomic<uint32_t> launchSeq{0};
 
