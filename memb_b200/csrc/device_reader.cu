@@ -37,6 +37,7 @@ std::atomic<int64_t> g_optUniformRows{1};
 std::atomic<int64_t> g_optTrainedRows{0};   // trained_rows_kernel: 0 never (default: measured slower than the ring kernel), 1 unions of trained readers in ONE launch, 2 single lookups too
 std::atomic<int64_t> g_optRowsWarps{0};     // cap on resident warps of trained_rows_kernel (0 = as many as fit)
 std::atomic<int64_t> g_optTma{1};           // ring kernel bulk-async staging: 0 off, 1 range decodes (one copy per tile) and long records, 2 one copy per row everywhere
+std::atomic<int64_t> g_optRecordAlign{1};   // fixed-stride records: stride a multiple of this many 16 B units (experiment: 2 = whole 32 B sectors)
 std::atomic<int64_t> g_optFixedRecords{1};  // 0: keep the offset table even when fixed-stride records would be cheap  // dense uniform lookups: 0 element walk, 1 uniform_rows_kernel unless levels is a power of two, 2 always
 
 struct StatusError {
@@ -480,7 +481,8 @@ void loadTrained(memb_b200_reader& r)
     // k-means + Huffman table are: 131 +- 2 B at 4 bits): row r at r * recUnits, no offset
     // table -- a lookup is id -> record instead of id -> offset -> row, and the 4 B gather
     // that cost a 64 B DRAM access per row is gone.  Otherwise rows back to back + offsets.
-    const uint32_t recUnits = std::max(maxRowUnits, 1u);
+    const uint32_t recAlign = static_cast<uint32_t>(g_optRecordAlign.load());
+    const uint32_t recUnits = (std::max(maxRowUnits, 1u) + recAlign - 1) / recAlign * recAlign;
     const bool fixed = g_optFixedRecords.load() && uint64_t(rows) * recUnits <= sumUnits + sumUnits / 4 + 4096;
     std::vector<uint32_t> rowOff16;
     uint64_t units = fixed ? uint64_t(std::max(rows, 1u)) * recUnits : 0;
@@ -567,7 +569,7 @@ void loadTrained(memb_b200_reader& r)
     p.lutMask = ((1u << lutBits) - 1) << padBits;
     p.symShift = symShift;
     p.codebookSize = codebookSize;
-    p.rowWords = maxRowUnits * K::TRAINED_UNIT_WORDS + 4;
+    p.rowWords = (fixed ? recUnits : maxRowUnits) * K::TRAINED_UNIT_WORDS + 4;  // every staged unit + the window's slack
     // slots of the 256-entry shared codebook past the last centroid hold +0.0: the row of a
     // missing word is "decoded" to that slot (symbol fields reach 63 with symShift 2, else 255)
     p.hasZeroSlot = codebookSize < (symShift == 2 ? 64u : 256u) ? 1u : 0u;
@@ -1343,6 +1345,8 @@ memb_b200_status memb_b200_set_option(const char* name, int64_t value)
             g_optRowsWarps = value;
         } else if (key == "trained_tma" && value >= 0 && value <= 2) {
             g_optTma = value;
+        } else if (key == "trained_record_align" && (value == 1 || value == 2 || value == 4)) {
+            g_optRecordAlign = value;
         } else if (key == "trained_fixed_records" && (value == 0 || value == 1)) {
             g_optFixedRecords = value;
         } else if (key == "host_pass_rows" && value >= 0) {
