@@ -3,7 +3,8 @@
 // (no other architecture, no dispatch).  See DESIGN.md for the HBM layout and
 // the roofline of every kernel.
 //
-//   L0 measure_rows / repack_rows   load time: exact row lengths, 16 B-aligned re-pack
+//   L0 measure_rows / repack_rows   load time: exact row lengths, re-pack into fixed-stride records (or 16 B-aligned rows)
+//      interleave_records           load time: the records once more, interleaved per 32 rows (one bulk copy per tile)
 //   L1 hash_build                   load time: vocabulary -> open-addressing hash
 //   K0 resolve_words                words -> row ids         (src/trained_compression.cpp:113-127)
 //   K1 trained_decode               ids -> fp32 rows         (src/trained_compression.cpp:129-136,
@@ -12,6 +13,8 @@
 //   K2 uniform_decode               ids -> fp32 rows         (src/uniform_compression.cpp:58-73)
 //   K3 full_gather                  ids -> fp32 rows         (src/full_compression.cpp:41-42)
 //   K4 = K1/K2/K3 with a fused ReadersUnion epilogue         (python/memb/readers_union.py:16-18,30-32)
+// trained_rows.cuh: trained_rows_kernel, whole-row tiles + multi-symbol LUT, a union of two trained
+// readers in one launch (measured slower, selectable); device_builder.cu: the GPU converter's kernels.
 #pragma once
 
 #include <cstdint>

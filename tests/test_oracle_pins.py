@@ -149,3 +149,20 @@ def test_oracle_and_reference_headers_agree_on_synthetic(oracle, ref_oracle, syn
         b = ref_oracle.open(syn.path).decode_range(0, 400)
         assert ref_oracle.uses_reference_codec and not oracle.uses_reference_codec
         assert bits_equal(a, b)
+
+
+def test_vectorised_packer_matches_the_bit_order_kat():
+    """tests/membfile_py.pack_rows_numpy (used for the bench's 16-bit-code table) packs exactly like pack_row,
+    which the bit-order KAT above pins (src/bit_stream_tests.cpp:31-59): MSB-first, zero padded to a byte."""
+    import membfile_py
+
+    rng = np.random.default_rng(3)
+    keys, lengths = list(range(17)), list(range(1, 17)) + [16]
+    weights = np.array([2.0 ** -n for n in lengths]) + 0.01
+    symbols = rng.choice(17, (257, 301), p=weights / weights.sum()).astype(np.uint8)
+    packed, offsets = membfile_py.pack_rows_numpy(symbols, keys, lengths, chunk_rows=50)
+    codes = membfile_py.canonical_codes(lengths)
+    code_of, len_of = dict(zip(keys, codes)), dict(zip(keys, lengths))
+    for r in range(len(symbols)):
+        end = int(offsets[r + 1]) if r + 1 < len(symbols) else len(packed)
+        assert bytes(packed[int(offsets[r]):end]) == membfile_py.pack_row(symbols[r], code_of, len_of), r
