@@ -218,6 +218,12 @@ memb_b200_status memb_b200_builder_add_words(memb_b200_builder* builder, const c
 memb_b200_status memb_b200_builder_set_device(memb_b200_builder* builder, int device);
 /* Builder::save — src/builder.cpp:64-68 */
 memb_b200_status memb_b200_builder_save(memb_b200_builder* builder, const char* path, unsigned num_threads);
+/* The Builder's 1-D k-means on its own (additive; host only, no device needed): KMeansClusterizer(clusters)
+ * .fit(data) then .predict(data) — src/kmeans.cpp:26-79 — so that the reference's own k-means test
+ * (src/kmeans_tests.cpp:9-38) can be replayed against it.  ids: n cluster indices; centroids: room for
+ * `clusters` floats, *num_centroids = how many survived the pruning of small clusters. */
+memb_b200_status memb_b200_kmeans_fit_predict(const float* data, uint64_t n, uint32_t clusters, uint8_t* ids,
+                                              float* centroids, uint32_t* num_centroids);
 /* availableCompressionStrategies() — src/compression_strategy.cpp:63-78; returns "full\0uniform\0trained\0\0" */
 const char* memb_b200_available_compression_strategies(void);
 

@@ -1991,6 +1991,23 @@ memb_b200_status memb_b200_builder_save(memb_b200_builder* builder, const char* 
     });
 }
 
+memb_b200_status memb_b200_kmeans_fit_predict(const float* data, uint64_t n, uint32_t clusters, uint8_t* ids,
+                                              float* centroids, uint32_t* num_centroids)
+{
+    return guarded([&] {
+        if (!data || !ids || !centroids || !num_centroids || n == 0 || clusters < 2 || clusters > 255) {
+            fail(MEMB_B200_ERR_ARGUMENT, "kmeans_fit_predict: bad argument");
+        }
+        KMeans1D km;
+        km.fit(data, n, clusters);
+        for (uint64_t i = 0; i < n; ++i) {
+            ids[i] = km.predictOne(data[i]);
+        }
+        *num_centroids = static_cast<uint32_t>(km.centroids.size());
+        std::copy(km.centroids.begin(), km.centroids.end(), centroids);
+    });
+}
+
 const char* memb_b200_available_compression_strategies(void)
 {
     return "full\0uniform\0trained\0";

@@ -166,3 +166,35 @@ def test_vectorised_packer_matches_the_bit_order_kat():
     for r in range(len(symbols)):
         end = int(offsets[r + 1]) if r + 1 < len(symbols) else len(packed)
         assert bytes(packed[int(offsets[r]):end]) == membfile_py.pack_row(symbols[r], code_of, len_of), r
+
+
+def test_builder_kmeans_on_the_references_own_case(abi):
+    """kMeansWork, src/kmeans_tests.cpp:9-38: three separated 1-D clusters, KMeansClusterizer(3).fit(data),
+    predict(data) must give exactly the expected cluster ids.  Replayed against the Builder's k-means
+    (memb_b200/csrc/builder.cpp, restated from src/kmeans.cpp:26-112) through memb_b200_kmeans_fit_predict --
+    the one reference-held vector that pins the write path's clustering."""
+    import ctypes
+
+    data, expected = [], []
+    for i in range(8):   # MIDDLE_CLUSTER_SIZE
+        data.append(-0.5 + i * 0.125)
+        expected.append(1)
+    for i in range(16):  # FIRST_CLUSTER_SIZE
+        data.append(-9 + i * 0.125)
+        expected.append(0)
+    for i in range(4):   # LAST_CLUSTER_SIZE
+        data.append(11.75 + i * 0.125)
+        expected.append(2)
+    values = np.array(data, np.float32)
+    ids = np.zeros(len(values), np.uint8)
+    centroids = np.zeros(3, np.float32)
+    count = ctypes.c_uint32(0)
+    fn = abi.lib.memb_b200_kmeans_fit_predict
+    fn.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
+                   ctypes.POINTER(ctypes.c_uint32)]
+    abi.check(fn(values.ctypes.data, len(values), 3, ids.ctypes.data, centroids.ctypes.data, ctypes.byref(count)))
+    assert ids.tolist() == expected
+    assert count.value == 3 and np.all(np.diff(centroids) > 0)
+    # the centroids are the cluster means (running-mean update, src/kmeans.cpp:86-102), to float rounding
+    means = [np.mean(values[8:24]), np.mean(values[:8]), np.mean(values[24:])]
+    assert np.allclose(centroids, means, rtol=1e-5)
