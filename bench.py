@@ -678,6 +678,12 @@ def run_b200(args):
         if not args.no_sweep:
             extra["configs3_sweep"] = sweep(args, ctx)
         line["extra"] = extra
+        extras_ok = (extra["configs0_small_batch"]["parity"] and extra["gpu_converter"]["files_byte_identical"] and
+                     extra["resolve_kernel_device_only"]["ids_match_host_resolve"] and
+                     all(t["parity"] for t in extra.get("configs3_sweep", {}).values()))
+        line["parity"]["extras"] = bool(extras_ok)
+        parity = parity and bool(extras_ok)
+        line["parity_vs_oracle"] = parity
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
