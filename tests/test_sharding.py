@@ -111,3 +111,34 @@ def test_decode_range_sharded_single_process(synthetic):
     torch.cuda.synchronize()
     assert span == (0, len(ids))
     assert np.array_equal(rows.cpu().numpy().view(np.uint32), reader.batch_embedding_ids(ids).view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_decode_range_gathered_and_out_validation(oracle, synthetic):
+    """decode_range_gathered decodes straight into this rank's slot of the gathered buffer (no send copy);
+    with one process the slot is the whole buffer.  `out=` arguments are validated instead of being written
+    out of bounds."""
+    import torch
+
+    import memb_b200
+    from memb_b200.sharding import decode_range_gathered, decode_range_sharded
+
+    syn = synthetic("trained", 4, rows=3000, dim=300, seed=11)
+    reader = memb_b200.Reader(syn.path)
+    want = oracle.open(syn.path).decode_range(0, 3000)
+    got = decode_range_gathered(reader)
+    torch.cuda.synchronize()
+    assert np.array_equal(got.cpu().numpy().view(np.uint32), want.view(np.uint32))
+    part = decode_range_gathered(reader, 100, 1133)
+    torch.cuda.synchronize()
+    assert np.array_equal(part.cpu().numpy().view(np.uint32), want[100:1133].view(np.uint32))
+    reuse = torch.empty((3000, 300), dtype=torch.float32, device="cuda")
+    assert decode_range_gathered(reader, out=reuse).data_ptr() == reuse.data_ptr()
+    for bad in (torch.empty((2999, 300), dtype=torch.float32, device="cuda"),
+                torch.empty((3000, 300), dtype=torch.float64, device="cuda"),
+                torch.empty((3000, 600), dtype=torch.float32, device="cuda")[:, ::2],
+                torch.empty((3000, 300), dtype=torch.float32)):
+        with pytest.raises(ValueError):
+            decode_range_sharded(reader, out=bad)
+        with pytest.raises(ValueError):
+            decode_range_gathered(reader, out=bad)
