@@ -32,7 +32,7 @@ std::atomic<int64_t> g_optWarps{0};
 std::atomic<int64_t> g_optGeneric{0};
 std::atomic<int64_t> g_optPassRows{0};
 std::atomic<int64_t> g_optSymAverage{1};
-std::atomic<int64_t> g_optPairTable{1};     // average through symbol words: merged values from a pair table when the codebooks are small
+std::atomic<int64_t> g_optPairTable{2};     // average through symbol words: 0 two gathers, 1 pair table (small codebooks), 2 + predicate-free middle-chunk flush
 std::atomic<int64_t> g_optUniformRows{1};
 std::atomic<int64_t> g_optTrainedRows{0};   // trained_rows_kernel: 0 never (default: measured slower than the ring kernel), 1 unions of trained readers in ONE launch, 2 single lookups too
 std::atomic<int64_t> g_optRowsWarps{0};     // cap on resident warps of trained_rows_kernel (0 = as many as fit)
@@ -1257,6 +1257,7 @@ void launchUnion(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_m
             if (lay.end - r1.smemBase <= r1.smemOptin) {
                 specs[1].pairEntries = entries;
                 specs[1].pairLog2 = log2Stride;
+                specs[1].straightPairs = g_optPairTable.load() == 2 ? 1u : 0u;
             }
         }
     }
@@ -1346,7 +1347,7 @@ memb_b200_status memb_b200_set_option(const char* name, int64_t value)
             g_optGeneric = value;
         } else if (key == "union_symbol_average" && (value == 0 || value == 1)) {
             g_optSymAverage = value;
-        } else if (key == "union_pair_table" && (value == 0 || value == 1)) {
+        } else if (key == "union_pair_table" && value >= 0 && value <= 2) {
             g_optPairTable = value;
         } else if (key == "uniform_rows_kernel" && value >= 0 && value <= 2) {
             g_optUniformRows = value;

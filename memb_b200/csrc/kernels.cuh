@@ -76,6 +76,7 @@ struct OutputSpec {
     // centroids + add + scale.  Same device arithmetic as the two-gather flush: bit-identical.
     uint32_t pairEntries = 0;            // 0: two-gather flush
     uint32_t pairLog2 = 0;               // log2 of the table's row stride (>= size1 + 1)
+    uint32_t straightPairs = 0;          // middle chunks take the predicate-free pair flush (option union_pair_table = 2, default)
 };
 
 // Where the 16 B unit `unit` of output row i goes (see OutputSpec::sideHead).
@@ -681,6 +682,19 @@ __device__ __forceinline__ float4 gatherPairs(uint32_t pairBase, uint32_t f0, ui
     v.w = ldsF32(pairBase + ((f0 >> 24) << sh0) + ((f1 >> 24) << sh1));
     return v;
 }
+// The same through 16-bit lanes: two elements per ALU instruction.  e = field bytes spread to 16-bit
+// halves (PRMT), offset pair = e0 * m0 + e1 * m1 (no carry between the halves: the table is < 64 KB).
+__device__ __forceinline__ float4 gatherPairsWide(uint32_t pairBase, uint32_t f0, uint32_t f1, uint32_t m0, uint32_t m1)
+{
+    const uint32_t lo = __byte_perm(f0, 0u, 0x4140) * m0 + __byte_perm(f1, 0u, 0x4140) * m1;  // elements 0, 1
+    const uint32_t hi = __byte_perm(f0, 0u, 0x4342) * m0 + __byte_perm(f1, 0u, 0x4342) * m1;  // elements 2, 3
+    float4 v;
+    v.x = ldsF32(pairBase + (lo & 0xffffu));
+    v.y = ldsF32(pairBase + (lo >> 16));
+    v.z = ldsF32(pairBase + (hi & 0xffffu));
+    v.w = ldsF32(pairBase + (hi >> 16));
+    return v;
+}
 __device__ __forceinline__ uint32_t ldU32If(bool pred, const uint32_t* ptr)
 {
     uint32_t v = 0;
@@ -1222,12 +1236,11 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
             const uint32_t word0 = (c0 / 4) & (TRAINED_RING_UNITS - 1);  // ring position of this chunk's first word
             // SYM == 2: the symbol words this chunk's flush adds to are LOADED here, before the decode, and
             // consumed after it (eight registers per lane; fp32 running sums would be 32: L2 prefetch only).
-            // Measured r02 on the two-reader average, 1 M Zipf words: 0.787 ms two-gather flush -> 0.764 with
-            // the pair table -> 0.762 with these loads ahead.  The launch's cost is its flush's INSTRUCTIONS
-            // (ncu: 226 M warp instructions against 119 M for a plain decode; 43 M bank conflicts on the pair
-            // table, which spans every bank, against none on a 16-entry codebook) -- yet a predicate-free
-            // straight-line flush for middle chunks, as the plain path has, was SLOWER (0.83-0.91 ms): its
-            // burst of 32 gathers + 8 stores per lane queues in front of the other warps' LUT loads.
+            // Measured r02 on the two-reader average, 1 M Zipf words (stable once the stream-ordered pool kept
+            // its memory): 0.777 ms two-gather flush -> 0.752 with the pair table -> 0.723 with the
+            // predicate-free middle-chunk flush below.  The launch's cost is its flush's INSTRUCTIONS (ncu:
+            // 226 M warp instructions against 119 M for a plain decode, ~55 per flushed unit, half of them
+            // pair-table address math; 43 M bank conflicts on the table, which spans every bank).
             uint32_t symAhead[TRAINED_CHUNK_UNITS];
             if (RMW && fastFlush) {
                 // the flush of this chunk will read these 16 B units of the running sum
@@ -1290,7 +1303,19 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                 const bool last = c0 + TRAINED_CHUNK >= dim;
                 const int unitsBefore = int(c0 / 4);
                 const int unitsAfter = int((c0 + nsym) / 4);
-                if (fastFlush && RMW) {
+                if (SYM == 2 && fastFlush && RMW && !last && c0 != 0 && o.pairEntries && o.straightPairs) {
+                    // pair-table average, middle chunk: every unit of the lagged window exists -- no predicates,
+                    // no pass loop, address math on two elements per instruction (gatherPairsWide)
+                    const uint32_t m0 = 1u << (o.pairLog2 + o.symFieldShift), m1 = SMALLCB ? 1u : 4u;
+#pragma unroll
+                    for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
+                        const int a = int((aBase + it * aStep) & 7u);
+                        const int j = unitsBefore - a + int(fq);
+                        const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
+                        stcsF4(reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j,
+                               gatherPairsWide(lay.lut2, symAhead[it], s4, m0, m1));
+                    }
+                } else if (fastFlush && RMW) {
                     // average epilogue, straight-line: the running sums of the chunk were
                     // pulled into L2 while the chunk was being decoded; load them all, then
                     // gather, add (divide for the last reader) and store.  A second pass
