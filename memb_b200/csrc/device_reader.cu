@@ -763,8 +763,10 @@ void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t
             configured |= bit;
         }
     }
-    uint32_t* counter = r.dTileCounters + (const_cast<memb_b200_reader&>(r).launchSeq++ % memb_b200_reader::TILE_COUNTERS);
-    CUDA_CHECK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), stream));
+    // a {ticket, done} pair of the ring; the kernel leaves both words zero (no memset per launch)
+    // (lower half of the ring: pairs; upper half: the single-word, memset-per-launch slots of the other kernels)
+    uint32_t* counter = r.dTileCounters +
+                        2 * (const_cast<memb_b200_reader&>(r).launchSeq++ % (memb_b200_reader::TILE_COUNTERS / 4));
     kernel<<<grid, block, smemBytes, stream>>>(p, ids, rowBegin, n, o, epi, counter);
 }
 
@@ -914,7 +916,8 @@ void launchRowsKernel(const memb_b200_reader& r0, const RowsPlan& plan, const in
     if (tiles + 4ull * grid * plan.warps >= 0xffffffffull) {
         fail(MEMB_B200_ERR_ARGUMENT, "decode: too many rows in one call");
     }
-    uint32_t* counter = r0.dTileCounters + (const_cast<memb_b200_reader&>(r0).launchSeq++ % memb_b200_reader::TILE_COUNTERS);
+    uint32_t* counter = r0.dTileCounters + memb_b200_reader::TILE_COUNTERS / 2 +
+                        (const_cast<memb_b200_reader&>(r0).launchSeq++ % (memb_b200_reader::TILE_COUNTERS / 2));
     CUDA_CHECK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), stream));
     kernel<<<grid, plan.warps * 32, plan.smemBytes, stream>>>(plan.P, ids, idStride, rowBegin, n, out, counter);
     ++g_launches;
@@ -1099,7 +1102,8 @@ void launchDecode(const memb_b200_reader& r, const int32_t* ids, uint32_t rowBeg
                 }
                 constexpr unsigned W = K::UNIFORM_ROWS_WARPS;  // one 32-row group per warp at a time
                 const unsigned grid = static_cast<unsigned>(std::min<uint64_t>(((n + 31) / 32 + W - 1) / W, uint64_t(r.numSMs) * perSM));
-                uint32_t* counter = r.dTileCounters + (const_cast<memb_b200_reader&>(r).launchSeq++ % memb_b200_reader::TILE_COUNTERS);
+                uint32_t* counter = r.dTileCounters + memb_b200_reader::TILE_COUNTERS / 2 +
+                                    (const_cast<memb_b200_reader&>(r).launchSeq++ % (memb_b200_reader::TILE_COUNTERS / 2));
                 CUDA_CHECK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), stream));
                 kernel<<<grid, W * 32, 0, stream>>>(r.uniform, ids, rowBegin, n, o.out, counter);
             };
@@ -1439,6 +1443,7 @@ memb_b200_status memb_b200_open(const char* path, int device, unsigned num_threa
         // work counters of the dynamically scheduled kernels (trained tiles, uniform row groups)
         CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&reader->dTileCounters),
                               memb_b200_reader::TILE_COUNTERS * sizeof(uint32_t)));
+        CUDA_CHECK(cudaMemset(reader->dTileCounters, 0, memb_b200_reader::TILE_COUNTERS * sizeof(uint32_t)));
         const auto t1 = std::chrono::steady_clock::now();
         buildVocabulary(*reader);
         reader->stats.upload_ms += msSince(t1);

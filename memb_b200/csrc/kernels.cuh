@@ -1490,6 +1490,17 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     if (TMA == 1) {
         mbarWait(mbar, mbarPhase);  // the copies issued for the tile after the last: never leave with them in flight
     }
+    // The tile counter is handed back CLEAN: tileCounter[1] counts the warps that are through (every warp of the
+    // grid gets here, all of its ticket draws behind it); atomicInc wraps it to 0 for the last one, which resets the
+    // ticket word.  Saves the cudaMemsetAsync that used to precede every launch (2-3 us of stream time: 3 % of a
+    // 94 us strong-scaling launch at 8 GPUs).
+    __syncwarp();
+    if (lane == 0) {
+        __threadfence();
+        if (atomicInc(tileCounter + 1, totalWarps - 1) == totalWarps - 1) {
+            atomicExch(tileCounter, 0u);
+        }
+    }
 }
 
 // Generic trained decode for shapes the tiled kernel does not take (dim > 4095
