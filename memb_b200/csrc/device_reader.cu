@@ -32,7 +32,7 @@ std::atomic<int64_t> g_optWarps{0};
 std::atomic<int64_t> g_optGeneric{0};
 std::atomic<int64_t> g_optPassRows{0};
 std::atomic<int64_t> g_optSymAverage{1};
-std::atomic<int64_t> g_optPairTable{2};     // average through symbol words: 0 two gathers, 1 pair table (small codebooks), 2 + predicate-free middle-chunk flush
+std::atomic<int64_t> g_optPairTable{3};     // average through symbol words: 0 two gathers, 1 pair table (small codebooks), 2 + predicate-free middle-chunk flush, 3 + one table copy per bank
 std::atomic<int64_t> g_optUniformRows{1};
 std::atomic<int64_t> g_optTrainedRows{0};   // trained_rows_kernel: 0 never (default: measured slower than the ring kernel), 1 unions of trained readers in ONE launch, 2 single lookups too
 std::atomic<int64_t> g_optRowsWarps{0};     // cap on resident warps of trained_rows_kernel (0 = as many as fit)
@@ -743,7 +743,7 @@ void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t
     const K::TrainedLayout lay = K::trainedLayout(
         r.smemBase, K::trainedLutBytes(p.lutBits, p.lutReplicas),
         K::trainedWarpBytes(p.rowWords, TMA ? K::trainedLandingBytes(p.recUnits) : 0u), r.trainedWarps,
-        SYM == 2 ? o.pairEntries : p.lut2Entries);
+        SYM == 2 ? o.pairEntries * o.pairReplicas : p.lut2Entries);
     const size_t smemBytes = lay.end - r.smemBase;
     const uint64_t tiles = (n + 31) / 32;
     const unsigned grid = static_cast<unsigned>(
@@ -1253,16 +1253,26 @@ void launchUnion(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_m
         while ((1u << log2Stride) < r1.trained.codebookSize + 1) {
             ++log2Stride;
         }
-        const uint32_t entries = (readers[0]->trained.codebookSize + 1) << log2Stride;
-        if (g_optPairTable.load() && entries <= 4096) {
+        const int64_t flavour = g_optPairTable.load();
+        auto fits = [&](uint32_t tableWords) {
             const K::TrainedLayout lay = K::trainedLayout(
                 r1.smemBase, K::trainedLutBytes(r1.trained.lutBits, r1.trained.lutReplicas),
-                K::trainedWarpBytes(r1.trained.rowWords, 0u), r1.trainedWarps, entries);
-            if (lay.end - r1.smemBase <= r1.smemOptin) {
-                specs[1].pairEntries = entries;
-                specs[1].pairLog2 = log2Stride;
-                specs[1].straightPairs = g_optPairTable.load() == 2 ? 1u : 0u;
-            }
+                K::trainedWarpBytes(r1.trained.rowWords, 0u), r1.trainedWarps, tableWords);
+            return lay.end - r1.smemBase <= r1.smemOptin;
+        };
+        // one copy of the table per bank (flavour 3): exact row stride, every byte offset within 16 bits
+        const uint32_t exact = (readers[0]->trained.codebookSize + 1) * (r1.trained.codebookSize + 1);
+        const uint32_t entries = (readers[0]->trained.codebookSize + 1) << log2Stride;
+        if (flavour == 3 && exact * 128u <= 65536u && fits(exact * 32u)) {
+            specs[1].pairEntries = exact;
+            specs[1].pairStride = r1.trained.codebookSize + 1;
+            specs[1].pairReplicas = 32;
+            specs[1].straightPairs = 1u;
+        } else if (flavour && entries <= 4096 && fits(entries)) {
+            specs[1].pairEntries = entries;
+            specs[1].pairStride = 1u << log2Stride;
+            specs[1].pairReplicas = 1;
+            specs[1].straightPairs = flavour >= 2 ? 1u : 0u;
         }
     }
     for (uint32_t k = 0; k < R; ++k) {
@@ -1351,7 +1361,7 @@ memb_b200_status memb_b200_set_option(const char* name, int64_t value)
             g_optGeneric = value;
         } else if (key == "union_symbol_average" && (value == 0 || value == 1)) {
             g_optSymAverage = value;
-        } else if (key == "union_pair_table" && value >= 0 && value <= 2) {
+        } else if (key == "union_pair_table" && value >= 0 && value <= 3) {
             g_optPairTable = value;
         } else if (key == "uniform_rows_kernel" && value >= 0 && value <= 2) {
             g_optUniformRows = value;

@@ -74,8 +74,12 @@ struct OutputSpec {
     // builds T[s0][s1] = epilogue(c0[s0], c1[s1]) once per CTA ((size0 + 1) x pairStride entries, the
     // +0.0 slots of missing words included) and the flush gathers ONE value per element instead of two
     // centroids + add + scale.  Same device arithmetic as the two-gather flush: bit-identical.
-    uint32_t pairEntries = 0;            // 0: two-gather flush
-    uint32_t pairLog2 = 0;               // log2 of the table's row stride (>= size1 + 1)
+    // pairReplicas == 32: one copy of the table per shared-memory bank (entry i of lane l at word i * 32 + l), like
+    // the LUT -- the gathers of a warp never conflict (a single copy spans every bank: ncu r02 counted 43 M
+    // bank-conflict wavefronts of 75 M in the average's second launch).  Needs entries * 128 B <= 64 KB.
+    uint32_t pairEntries = 0;            // (size0 + 1) * pairStride logical entries; 0: two-gather flush
+    uint32_t pairStride = 0;             // entries per s0 row (>= size1 + 1)
+    uint32_t pairReplicas = 1;           // 1 or 32
     uint32_t straightPairs = 0;          // middle chunks take the predicate-free pair flush (option union_pair_table = 2, default)
 };
 
@@ -639,6 +643,54 @@ __device__ __forceinline__ void flushStoreF4If(uint32_t multicast, bool pred, vo
     (void)multicast;
     stcsF4If(pred, ptr, v);
 }
+// The stores of a row's FIRST and LAST chunk: they hold the row's two partial 128 B lines, and for every
+// other row (1200 B rows) a 32 B sector shared with the neighbouring row, whose half arrives a tile time
+// (~14 us, ~55 MB of other stores) later.  Build switch MEMB_BOUNDARY_STORE: 0 = the streaming store like
+// everything else, 1 = plain st.global (evict-normal beside the evict-first body), 2 = L2::evict_last
+// cache hint on both, 3 = evict_last on the first chunk only (within a tile the head of row r is written
+// at the START of the tile and the tail of row r - 1, which completes the line, at its END), 4 = on the
+// last chunk only (control) -- does the half-written sector survive in L2 until its other half arrives?
+// Measured r02, 1 M random ids, interleaved repeats of 200 steps (each figure repeats to 0.1 % on one box;
+// boxes differ by more than the effect): box A 0.2959 (0) / 0.3044 (1) / 0.2864 (2); boxes B, C 0.2981-0.2988
+// (0) / 0.2974-0.2980 (2) / 0.2963-0.2968 (3) / 0.2999 (4).  Sequential ids: no difference.  Default 3.
+#ifndef MEMB_BOUNDARY_STORE
+#define MEMB_BOUNDARY_STORE 3
+#endif
+__device__ __forceinline__ uint64_t boundaryStorePolicy()
+{
+    uint64_t policy = 0;
+#if MEMB_BOUNDARY_STORE >= 2
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(policy));
+#endif
+    return policy;
+}
+// FIRST: the store belongs to the row's first chunk (else to its last)
+template <bool FIRST>
+__device__ __forceinline__ void boundaryStoreF4If(uint64_t policy, bool pred, void* ptr, float4 v)
+{
+    constexpr bool hinted = MEMB_BOUNDARY_STORE == 2 || (MEMB_BOUNDARY_STORE == 3 && FIRST) || (MEMB_BOUNDARY_STORE == 4 && !FIRST);
+    if (MEMB_BOUNDARY_STORE == 1) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "setp.ne.u32 p, %5, 0;\n"
+            "@p st.global.v4.f32 [%0], {%1, %2, %3, %4};\n"
+            "}\n" ::"l"(ptr),
+            "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(static_cast<uint32_t>(pred))
+            : "memory");
+    } else if (hinted) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "setp.ne.u32 p, %5, 0;\n"
+            "@p st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %6;\n"
+            "}\n" ::"l"(ptr),
+            "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(static_cast<uint32_t>(pred)), "l"(policy)
+            : "memory");
+    } else {
+        stcsF4If(pred, ptr, v);
+    }
+}
 
 // Four centroids for the four symbol fields packed in s4.  cb = shared address of
 // the codebook (1 KiB aligned).  SMALLCB: a field already is the byte offset
@@ -672,14 +724,14 @@ __device__ __forceinline__ float4 gatherCentroidsShift(uint32_t cb, uint32_t s4,
     return v;
 }
 // Four merged values for four symbol pairs: f0 / f1 = packed symbol fields of reader 0 / reader 1,
-// sh0 / sh1 turn a field into its byte offset contribution (OutputSpec::pairEntries).
-__device__ __forceinline__ float4 gatherPairs(uint32_t pairBase, uint32_t f0, uint32_t f1, uint32_t sh0, uint32_t sh1)
+// m0 / m1 turn a field into its byte offset contribution (OutputSpec::pairEntries).
+__device__ __forceinline__ float4 gatherPairs(uint32_t pairBase, uint32_t f0, uint32_t f1, uint32_t m0, uint32_t m1)
 {
     float4 v;
-    v.x = ldsF32(pairBase + ((f0 & 0xffu) << sh0) + ((f1 & 0xffu) << sh1));
-    v.y = ldsF32(pairBase + (((f0 >> 8) & 0xffu) << sh0) + (((f1 >> 8) & 0xffu) << sh1));
-    v.z = ldsF32(pairBase + (((f0 >> 16) & 0xffu) << sh0) + (((f1 >> 16) & 0xffu) << sh1));
-    v.w = ldsF32(pairBase + ((f0 >> 24) << sh0) + ((f1 >> 24) << sh1));
+    v.x = ldsF32(pairBase + (f0 & 0xffu) * m0 + (f1 & 0xffu) * m1);
+    v.y = ldsF32(pairBase + ((f0 >> 8) & 0xffu) * m0 + ((f1 >> 8) & 0xffu) * m1);
+    v.z = ldsF32(pairBase + ((f0 >> 16) & 0xffu) * m0 + ((f1 >> 16) & 0xffu) * m1);
+    v.w = ldsF32(pairBase + (f0 >> 24) * m0 + (f1 >> 24) * m1);
     return v;
 }
 // The same through 16-bit lanes: two elements per ALU instruction.  e = field bytes spread to 16-bit
@@ -910,7 +962,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     const uint32_t base = smemAddr(smem);
     const uint32_t perWarp = trainedWarpBytes(p.rowWords, TMA ? trainedLandingBytes(p.recUnits) : 0u);
     // (the region behind the codebooks holds the second-level table, or -- SYM == 2, never with long codes -- the pair table)
-    const TrainedLayout lay = trainedLayout(base, lutBytes, perWarp, warpsPerCta, SYM == 2 ? o.pairEntries : p.lut2Entries);
+    const TrainedLayout lay = trainedLayout(base, lutBytes, perWarp, warpsPerCta, SYM == 2 ? o.pairEntries * o.pairReplicas : p.lut2Entries);
     {
         uint32_t dynBytes;
         asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dynBytes));
@@ -952,10 +1004,19 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         if (SYM == 2) {
             float* pairS = reinterpret_cast<float*>(smem + (lay.lut2 - base));
             for (uint32_t i = threadIdx.x; i < o.pairEntries; i += blockDim.x) {
-                const uint32_t s0 = i >> o.pairLog2, s1 = i & ((1u << o.pairLog2) - 1u);
+                const uint32_t s0 = i / o.pairStride, s1 = i % o.pairStride;
                 const float c0 = s0 < o.symCodebookSize ? o.symCodebook[s0] : 0.f;
                 const float c1 = s1 < p.codebookSize ? p.codebook[s1] : 0.f;
-                pairS[i] = applyEpilogue(c1, c0, epi, o.divisor);  // c0 + c1 in reader order, / R for the last reader
+                const float t = applyEpilogue(c1, c0, epi, o.divisor);  // c0 + c1 in reader order, / R for the last reader
+                if (o.pairReplicas == 1) {
+                    pairS[i] = t;
+                } else {
+                    float4* dst = reinterpret_cast<float4*>(pairS + i * WARP);  // (lay.lut2 is 1 KiB aligned: replica l sits in bank l)
+#pragma unroll
+                    for (uint32_t q = 0; q < WARP / 4; ++q) {
+                        dst[q] = make_float4(t, t, t, t);
+                    }
+                }
             }
         }
         if (ESCAPE) {
@@ -988,6 +1049,8 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     d.lut2 = lay.lut2;
     d.padL = p.padBits + p.lutBits;
     const uint32_t tileLane = tileRowBase(tile, lane);
+    const uint64_t boundaryPolicy = boundaryStorePolicy();
+    const uint32_t pairBase = lay.lut2 + (SYM == 2 && o.pairReplicas != 1 ? lane * 4u : 0u);  // lane l reads bank l
     // The flush reads ring slots it then does not store (units before the row in the
     // first chunk, units past it in the last).  With SMALLCB a symbol byte IS a shared
     // address offset, so those slots must never hold anything but multiples of 4.
@@ -1306,14 +1369,15 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                 if (SYM == 2 && fastFlush && RMW && !last && c0 != 0 && o.pairEntries && o.straightPairs) {
                     // pair-table average, middle chunk: every unit of the lagged window exists -- no predicates,
                     // no pass loop, address math on two elements per instruction (gatherPairsWide)
-                    const uint32_t m0 = 1u << (o.pairLog2 + o.symFieldShift), m1 = SMALLCB ? 1u : 4u;
+                    const uint32_t m0 = (o.pairStride * o.pairReplicas) << o.symFieldShift;
+                    const uint32_t m1 = o.pairReplicas * (SMALLCB ? 1u : 4u);
 #pragma unroll
                     for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
                         const int a = int((aBase + it * aStep) & 7u);
                         const int j = unitsBefore - a + int(fq);
                         const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
                         stcsF4(reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j,
-                               gatherPairsWide(lay.lut2, symAhead[it], s4, m0, m1));
+                               gatherPairsWide(pairBase, symAhead[it], s4, m0, m1));
                     }
                 } else if (fastFlush && RMW) {
                     // average epilogue, straight-line: the running sums of the chunk were
@@ -1345,14 +1409,22 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
                             float4 v;
                             if (SYM == 2 && o.pairEntries) {
-                                v = gatherPairs(lay.lut2, __float_as_uint(old[it].x), s4, o.pairLog2 + o.symFieldShift,
-                                                SMALLCB ? 0u : 2u);
+                                v = gatherPairs(pairBase, __float_as_uint(old[it].x), s4,
+                                                (o.pairStride * o.pairReplicas) << o.symFieldShift,
+                                                o.pairReplicas * (SMALLCB ? 1u : 4u));
                             } else {
                                 const float4 sum = SYM == 2 ? gatherCentroidsShift(cb0, __float_as_uint(old[it].x), o.symFieldShift)
                                                             : old[it];
                                 v = applyEpilogue4(gatherCentroids<SMALLCB>(cb, s4), sum, epi, o.divisor);
                             }
-                            stcsF4If(j >= 0 && j < end, reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j, v);
+                            float4* const dst = reinterpret_cast<float4*>(rowPtr0 + it * TRAINED_FLUSH_ROWS * rowBytes) + j;
+                            if (c0 == 0) {  // (warp-uniform)
+                                boundaryStoreF4If<true>(boundaryPolicy, j >= 0 && j < end, dst, v);
+                            } else if (last) {
+                                boundaryStoreF4If<false>(boundaryPolicy, j >= 0 && j < end, dst, v);
+                            } else {
+                                stcsF4If(j >= 0 && j < end, dst, v);
+                            }
                         }
                     }
                 } else if (fastFlush) {
@@ -1389,7 +1461,11 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             if (SIDE) {
                                 dst = redirectUnit(o, dst, row0 + it * TRAINED_FLUSH_ROWS + fr, static_cast<uint32_t>(j), dim / 4 - 1);
                             }
-                            flushStoreF4If(o.multicast, j >= 0 && j < end, dst, v);
+                            if (c0 == 0) {  // (warp-uniform)
+                                boundaryStoreF4If<true>(boundaryPolicy, j >= 0 && j < end, dst, v);
+                            } else {
+                                boundaryStoreF4If<false>(boundaryPolicy, j >= 0 && j < end, dst, v);
+                            }
                         }
                         if (last) {
 #pragma unroll
@@ -1406,7 +1482,11 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                                 if (SIDE) {
                                     dst = redirectUnit(o, dst, row0 + it * TRAINED_FLUSH_ROWS + fr, static_cast<uint32_t>(j2), dim / 4 - 1);
                                 }
-                                flushStoreF4If(o.multicast, j2 < unitsAfter, dst, u);
+                                if (c0 == 0) {
+                                    boundaryStoreF4If<true>(boundaryPolicy, j2 < unitsAfter, dst, u);
+                                } else {
+                                    boundaryStoreF4If<false>(boundaryPolicy, j2 < unitsAfter, dst, u);
+                                }
                             }
                         }
                     }

@@ -747,14 +747,14 @@ def test_union_average_through_symbol_words(abi, oracle, synthetic, bits0, bits1
             assert bits_equal(helpers.union_lookup_words(abi, readers[:count], abi.AVERAGE, words, dim), want)
             abi.check(abi.lib.memb_b200_set_option(b"trained_rows_kernel", 0))
             # symbol words with the two-gather flush instead of the pair table
-            for flavour in (1, 0):  # pair table through the generic flush loop; no pair table
+            for flavour in (2, 1, 0):  # ONE table copy, predicate-free middle chunks; pair table through the generic flush loop; no pair table
                 abi.check(abi.lib.memb_b200_set_option(b"union_pair_table", flavour))
                 assert bits_equal(helpers.union_lookup_words(abi, readers[:count], abi.AVERAGE, words, dim), want)
-            abi.check(abi.lib.memb_b200_set_option(b"union_pair_table", 2))
+            abi.check(abi.lib.memb_b200_set_option(b"union_pair_table", 3))
             # plain read-modify-write of the output
             abi.check(abi.lib.memb_b200_set_option(b"union_symbol_average", 0))
             assert bits_equal(helpers.union_lookup_words(abi, readers[:count], abi.AVERAGE, words, dim), want)
         finally:
             abi.lib.memb_b200_set_option(b"union_symbol_average", 1)
-            abi.lib.memb_b200_set_option(b"union_pair_table", 2)
+            abi.lib.memb_b200_set_option(b"union_pair_table", 3)
             abi.lib.memb_b200_set_option(b"trained_rows_kernel", 0)
