@@ -814,6 +814,7 @@ def sharded_union(args, ctx):
     lo, hi = shard_range(total, rank, world)
     word_ids = perm[ranks[lo:hi]]
     n = hi - lo
+    distinct_fraction = float(len(np.unique(word_ids))) / max(n, 1)
     width = len("w%x" % (vocab - 1))
     table = np.array(["w%x" % i for i in range(vocab)], dtype="S%d" % width)
     blob, offsets = _memb.pack_words(table[word_ids])
@@ -860,13 +861,20 @@ def sharded_union(args, ctx):
             torch.cuda.synchronize()
             return both, dec, int(per_call), same_bits(want, out[:check].cpu().numpy())
 
-        # the fused ONE-launch kernel (trained_rows_kernel, option trained_rows_kernel = 1) beside the default
-        # (one ring-kernel launch per reader with fused merge epilogues): both measured, the faster is the default
+        # Every query decoded (union_dedup = 0) -- the kernels' own numbers: the fused ONE-launch kernel
+        # (trained_rows_kernel, option trained_rows_kernel = 1) beside one ring-kernel launch per reader with fused
+        # merge epilogues; both measured, the faster is the default.
+        _memb.set_option("union_dedup", 0)
         _memb.set_option("trained_rows_kernel", 1)
         one_ms, one_decode, one_launches, one_ok = measure()
         _memb.set_option("trained_rows_kernel", 0)
+        all_ms, all_decode, all_launches, all_ok = measure()
+        # The default (union_dedup = 1): a batch that repeats its words (this one is Zipf) has its DISTINCT id tuples
+        # decoded once and the rows copied out, when the cost model says the copy-out is cheaper than the decodes
+        # it saves (average: yes; concatenate of two readers: no -- same launches as above).
+        _memb.set_option("union_dedup", 1)
         ms, decode_only, launches_per_call, ok = measure()
-        ok = ok and one_ok
+        ok = ok and one_ok and all_ok
         # end to end: host blob -> device tensor through the words entry point (H2D + 2 x K0 + fused decode)
         packed = (blob, offsets)
         _memb.union_batch_embedding_into(impls, mode, packed, out.data_ptr(), n, True, stream)
@@ -885,6 +893,14 @@ def sharded_union(args, ctx):
                         "roofline_frac_decode_per_gpu": n * bytes_row / (decode_only / 1e3) / 1e9 / peak,
                         "roofline_frac_resolve_and_decode_per_gpu": n * (bytes_row + bytes_row_k0) / (ms / 1e3) / 1e9 / peak,
                         "words_api_host_blob_to_device_tensor_ms": e2e_ms, "out_columns": cols, "parity": ok,
+                        "distinct_tuples_path": {"taken": int(launches_per_call) > int(all_launches),
+                                                 "distinct_fraction_of_batch": distinct_fraction,
+                                                 "note": "option union_dedup (default 1): claim kernel over the id tuples, decode of the "
+                                                         "distinct ones, copy-out; two 4-byte host round trips decide"},
+                        "every_query_decoded": {"ms_decode": all_decode, "ms_resolve_and_decode": all_ms,
+                                                "launches_per_call": {"resolve": 2, "decode": int(all_launches) - 2},
+                                                "roofline_frac_decode_per_gpu": n * bytes_row / (all_decode / 1e3) / 1e9 / peak,
+                                                "parity": all_ok},
                         "one_launch_kernel": {"kernel": "trained_rows_kernel (option trained_rows_kernel=1)", "ms_decode": one_decode,
                                               "ms_resolve_and_decode": one_ms, "decode_launches": one_launches - 2,
                                               "roofline_frac_decode_per_gpu": n * bytes_row / (one_decode / 1e3) / 1e9 / peak,

@@ -34,6 +34,9 @@ std::atomic<int64_t> g_optPassRows{0};
 std::atomic<int64_t> g_optSymAverage{1};
 std::atomic<int64_t> g_optPairTable{3};     // average through symbol words: 0 two gathers, 1 pair table (small codebooks), 2 + predicate-free middle-chunk flush, 3 + one table copy per bank
 std::atomic<int64_t> g_optUniformRows{1};
+std::atomic<int64_t> g_optDedupCopy{1};     // copy-out of the distinct path: 1 copy_rows_kernel, 0 full_gather_kernel (the element walk)
+std::atomic<int64_t> g_optDedupKeys{1};     // distinct path, one or two readers: 1 the tuple is the slot's 64-bit key, 0 the generic claim (slots hold query indices)
+std::atomic<int64_t> g_optDedup{1};         // union lookups of batches that repeat their words: 0 decode every query, 1 decode distinct id tuples once when a sample says the batch repeats (default), 2 always take the distinct path (tests)
 std::atomic<int64_t> g_optTrainedRows{0};   // trained_rows_kernel: 0 never (default: measured slower than the ring kernel), 1 unions of trained readers in ONE launch, 2 single lookups too
 std::atomic<int64_t> g_optRowsWarps{0};     // cap on resident warps of trained_rows_kernel (0 = as many as fit)
 std::atomic<int64_t> g_optTma{1};           // ring kernel bulk-async staging: 0 off, 1 range decodes (one copy per tile) and long records, 2 one copy per row everywhere
@@ -1297,6 +1300,141 @@ void launchUnion(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_m
     }
 }
 
+// A batch that repeats its words (Zipf-distributed text; kernels.cuh "repeated queries"): the distinct id tuples
+// are decoded once into a temporary and full_gather_kernel copies the rows out.  Two host round trips of 4 bytes
+// (how many distinct tuples a 8192-query sample holds, then the whole batch) decide; a batch that does not repeat
+// pays the sample only.  Never under stream capture (the round trips synchronise), never for small batches.
+constexpr uint64_t DEDUP_MIN_QUERIES = 1u << 17;
+constexpr uint32_t DEDUP_SAMPLE = 8192;
+bool tryLaunchUnionDistinct(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_mode mode, const int32_t* dIds,
+                            uint64_t idStride, uint64_t first, uint64_t n, float* dOut, uint64_t unionDim,
+                            cudaStream_t stream)
+{
+    const int64_t opt = g_optDedup.load();
+    if (opt == 0 || n > 0x3fffffffull || (opt == 1 && n < DEDUP_MIN_QUERIES) || n < 2) {
+        return false;
+    }
+    cudaStreamCaptureStatus capturing = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &capturing) != cudaSuccess || capturing != cudaStreamCaptureStatusNone) {
+        cudaGetLastError();
+        return false;
+    }
+    const memb_b200_reader& r0 = *readers[0];
+    const uint32_t nq = static_cast<uint32_t>(n);
+    // Is there anything to win?  Per query, in HBM-byte equivalents measured on configs[4] (r02): decoding a trained
+    // row costs what ~1.65 x its fp32 bytes cost to move (0.30 ms per 1 M rows of 1200 B), uniform ~1.4 x, full 2 x
+    // (read + write); the copy-out moves the union row twice.  The distinct path pays d decodes + n copies (+ the
+    // claim, ~10 %): worth it below this fraction of distinct tuples.  Two trained readers: average 0.29 (the copy
+    // is half a decode), concatenate: never (the copy-out of 2400 B rows costs more than decoding them).
+    double decodeCost = 0;
+    for (uint32_t k = 0; k < R; ++k) {
+        const double perByte = readers[k]->file->storage == STORAGE_TRAINED ? 1.65 : readers[k]->file->storage == STORAGE_UNIFORM ? 1.4 : 2.0;
+        decodeCost += perByte * 4.0 * readers[k]->file->dim;
+    }
+    const double maxDistinctFraction = 0.9 - 2.0 * 4.0 * static_cast<double>(unionDim) / decodeCost;
+    if (opt == 1 && maxDistinctFraction < 0.05) {
+        return false;
+    }
+    uint32_t tableSlots = 1024;
+    while (tableSlots < 2 * n) {
+        tableSlots *= 2;
+    }
+    // one or two readers: the tuple is the slot's 64-bit key (dedup_claim64_kernel); more: slots hold query indices
+    const bool packed = R <= 2 && g_optDedupKeys.load() != 0;
+    // one block: count | slots (x2 when 64-bit, + compactOfSlot) | rep or slotOf | compact | distinct ids (R x n)
+    const uint64_t words = 64 + uint64_t(tableSlots) * (packed ? 3 : 1) + 2 * n + uint64_t(R) * n;
+    int32_t* block = nullptr;
+    CUDA_CHECK(cudaMallocAsync(reinterpret_cast<void**>(&block), words * 4, stream));
+    struct Release {
+        int32_t* p;
+        float* rows = nullptr;
+        cudaStream_t s;
+        ~Release()
+        {
+            if (rows) {
+                cudaFreeAsync(rows, s);
+            }
+            cudaFreeAsync(p, s);
+        }
+    } release{block, nullptr, stream};
+    uint32_t* dCount = reinterpret_cast<uint32_t*>(block);
+    int32_t* slots = block + 64;
+    int32_t* compactOfSlot = slots + 2 * uint64_t(tableSlots);  // (packed only)
+    int32_t* rep = slots + uint64_t(tableSlots) * (packed ? 3 : 1);
+    int32_t* compact = rep + n;
+    int32_t* distinctIds = compact + n;
+    const int32_t* ids = dIds + first;
+    auto claim = [&](uint32_t queries, uint32_t slotsUsed) -> uint32_t {
+        CUDA_CHECK(cudaMemsetAsync(dCount, 0, 4, stream));
+        CUDA_CHECK(cudaMemsetAsync(slots, 0xff, uint64_t(slotsUsed) * (packed ? 8 : 4), stream));
+        if (packed) {
+            K::dedup_claim64_kernel<<<(queries + 255) / 256, 256, 0, stream>>>(
+                ids, idStride, R, queries, readers[0]->file->rows, R > 1 ? readers[1]->file->rows : 0u,
+                reinterpret_cast<unsigned long long*>(slots), slotsUsed - 1, reinterpret_cast<uint32_t*>(rep), compactOfSlot,
+                compact, distinctIds, n, dCount);
+        } else {
+            K::dedup_claim_kernel<<<(queries + 255) / 256, 256, 0, stream>>>(ids, idStride, R, queries, slots, slotsUsed - 1,
+                                                                              rep, compact, distinctIds, n, dCount);
+        }
+        ++g_launches;
+        CUDA_CHECK(cudaGetLastError());
+        uint32_t count = 0;
+        CUDA_CHECK(cudaMemcpyAsync(&count, dCount, 4, cudaMemcpyDeviceToHost, stream));
+        CUDA_CHECK(cudaStreamSynchronize(stream));
+        return count;
+    };
+    if (opt == 1) {
+        const uint32_t sample = std::min<uint32_t>(nq, DEDUP_SAMPLE);
+        if (claim(sample, 4 * DEDUP_SAMPLE) > sample - sample / 8) {
+            return false;  // fewer than one query in eight repeats within the sample: decode them all
+        }
+    }
+    const uint32_t distinct = claim(nq, tableSlots);
+    if (opt == 1 && distinct > maxDistinctFraction * nq) {
+        return false;  // the copy-out of every row costs more than the repeats save
+    }
+    if (packed) {
+        K::dedup_follow64_kernel<<<(nq + 255) / 256, 256, 0, stream>>>(reinterpret_cast<const uint32_t*>(rep), compactOfSlot,
+                                                                       compact, nq);
+    } else {
+        K::dedup_follow_kernel<<<(nq + 255) / 256, 256, 0, stream>>>(rep, compact, nq);
+    }
+    ++g_launches;
+    CUDA_CHECK(cudaGetLastError());
+    CUDA_CHECK(cudaMallocAsync(reinterpret_cast<void**>(&release.rows), uint64_t(distinct) * unionDim * 4, stream));
+    launchUnion(readers, R, mode, distinctIds, n, 0, distinct, release.rows, unionDim, stream);
+    // the copy-out: K3 over the temporary (compact index = row of the temporary; every index is in range)
+    K::FullParams rows{release.rows, distinct, static_cast<uint32_t>(unionDim)};
+    K::OutputSpec o{dOut, unionDim, 0, 1.0f};
+    const bool vec = vec4Ok(static_cast<uint32_t>(unionDim), o);
+    const uint64_t elems = n * (vec ? unionDim / 4 : unionDim);
+    const unsigned grid = static_cast<unsigned>(std::min<uint64_t>((elems + 255) / 256, uint64_t(r0.numSMs) * 32));
+    if (vec && g_optDedupCopy.load()) {
+        const uint64_t groups = (n + K::COPY_ROWS - 1) / K::COPY_ROWS;  // one warp per group, 8 warps per block
+        const unsigned blocks = static_cast<unsigned>(std::min<uint64_t>((groups + 7) / 8, uint64_t(r0.numSMs) * 8));
+        auto go = [&](auto kernel) {
+            kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(release.rows), compact, n,
+                                               static_cast<uint32_t>(unionDim / 4), reinterpret_cast<float4*>(dOut));
+        };
+        g_optDedupCopy.load() == 2 ? go(K::copy_rows_kernel<true>) : go(K::copy_rows_kernel<false>);
+    } else if (vec) {
+        K::full_gather_kernel<true, K::EPI_WRITE><<<grid, 256, 0, stream>>>(rows, compact, 0, n, o);
+    } else {
+        K::full_gather_kernel<false, K::EPI_WRITE><<<grid, 256, 0, stream>>>(rows, compact, 0, n, o);
+    }
+    ++g_launches;
+    CUDA_CHECK(cudaGetLastError());
+    return true;
+}
+
+void launchUnionBatch(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_mode mode, const int32_t* dIds,
+                      uint64_t idStride, uint64_t first, uint64_t n, float* dOut, uint64_t unionDim, cudaStream_t stream)
+{
+    if (!tryLaunchUnionDistinct(readers, R, mode, dIds, idStride, first, n, dOut, unionDim, stream)) {
+        launchUnion(readers, R, mode, dIds, idStride, first, n, dOut, unionDim, stream);
+    }
+}
+
 uint64_t unionDimOf(memb_b200_reader* const* readers, uint32_t R, memb_b200_union_mode mode)
 {
     if (R < 2) {
@@ -1361,6 +1499,12 @@ memb_b200_status memb_b200_set_option(const char* name, int64_t value)
             g_optGeneric = value;
         } else if (key == "union_symbol_average" && (value == 0 || value == 1)) {
             g_optSymAverage = value;
+        } else if (key == "union_dedup" && value >= 0 && value <= 2) {
+            g_optDedup = value;
+        } else if (key == "union_dedup_keys" && (value == 0 || value == 1)) {
+            g_optDedupKeys = value;
+        } else if (key == "union_dedup_copy" && value >= 0 && value <= 2) {
+            g_optDedupCopy = value;
         } else if (key == "union_pair_table" && value >= 0 && value <= 3) {
             g_optPairTable = value;
         } else if (key == "uniform_rows_kernel" && value >= 0 && value <= 2) {
@@ -1836,7 +1980,7 @@ memb_b200_status memb_b200_union_decode_ids(memb_b200_reader* const* readers, ui
         }
         const int32_t* dIds = idsOnDevice(r, ids, ids_kind, n * num_readers, s);
         decodeTo(r, n, unionDim, out, out_kind, s, [&](uint64_t first, uint64_t count, float* dOut) {
-            launchUnion(readers, num_readers, mode, dIds, n, first, count, dOut, unionDim, s);
+            launchUnionBatch(readers, num_readers, mode, dIds, n, first, count, dOut, unionDim, s);
         });
         if (!async) {
             CUDA_CHECK(cudaStreamSynchronize(s));
@@ -1876,7 +2020,7 @@ static memb_b200_status unionLookupWords(memb_b200_reader* const* readers, uint3
             launchResolve(*readers[k], dQuery - base, dOffsets, n, dIds + k * n, s);
         }
         decodeTo(r, n, unionDim, out, out_kind, s, [&](uint64_t first, uint64_t count, float* dOut) {
-            launchUnion(readers, num_readers, mode, dIds, n, first, count, dOut, unionDim, s);
+            launchUnionBatch(readers, num_readers, mode, dIds, n, first, count, dOut, unionDim, s);
         });
         CUDA_CHECK(cudaStreamSynchronize(s));
     });

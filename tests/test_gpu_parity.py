@@ -758,3 +758,65 @@ def test_union_average_through_symbol_words(abi, oracle, synthetic, bits0, bits1
             abi.lib.memb_b200_set_option(b"union_symbol_average", 1)
             abi.lib.memb_b200_set_option(b"union_pair_table", 3)
             abi.lib.memb_b200_set_option(b"trained_rows_kernel", 0)
+
+
+@pytest.mark.parametrize("mode_name", ["average", "concatenate"])
+def test_union_distinct_tuples_path(abi, oracle, synthetic, mode_name):
+    """Batches that repeat their words: the distinct id tuples are decoded once and copied out
+    (union_dedup; kernels.cuh 'repeated queries').  Same bytes as decoding every query: forced on small
+    batches (all equal, all distinct, ragged sizes, missing words, three readers, mixed storages, arbitrary
+    id tuples through union_decode_ids), and the automatic choice on a 150 k-word batch over a 900-word
+    vocabulary."""
+    dim = 64
+    syns = [synthetic("trained", 4, rows=900, dim=dim, seed=61), synthetic("trained", 5, rows=800, dim=dim, seed=62),
+            synthetic("uniform", 8, rows=700, dim=dim, seed=63)]
+    readers = [abi.open_checked(s.path) for s in syns]
+    oracles = [oracle.open(s.path) for s in syns]
+    mode = abi.AVERAGE if mode_name == "average" else abi.CONCATENATE
+    rng = np.random.default_rng(5)
+
+    def merged(parts):
+        return np.mean(parts, axis=0) if mode_name == "average" else np.concatenate(parts, axis=-1)
+
+    def check_words(words, count):
+        want = merged([o.batch_embedding(words) for o in oracles[:count]])
+        got = helpers.union_lookup_words(abi, readers[:count], mode, words, want.shape[1])
+        assert bits_equal(got, want)
+
+    try:
+        abi.check(abi.lib.memb_b200_set_option(b"union_dedup", 2))  # always
+        launches = abi.lib.memb_b200_launch_count()
+        for count in (2, 3):
+            zipf = sum([queries_for(s, rng, 40) for s in syns], [])
+            check_words([zipf[i] for i in rng.zipf(1.3, 1537) % len(zipf)], count)   # heavy repeats
+            check_words([syns[0].words[7]] * 333, count)                              # one word only
+            check_words(["absent"] * 65, count)                                       # missing everywhere
+            check_words(sorted(set(queries_for(syns[1], rng, 500))), count)           # no repeats at all
+            check_words(queries_for(syns[0], rng, 2), count)
+        assert abi.lib.memb_b200_launch_count() > launches
+        # id tuples that no word would produce (the ids entry point takes any): equal tuples share a row, others do not
+        ids = np.stack([rng.integers(-2, 12, 4000), rng.integers(-1, 9, 4000)]).astype(np.int32)
+        parts = [o.batch_ids(ids[k]) for k, o in enumerate(oracles[:2])]
+        assert bits_equal(helpers.union_decode_ids(abi, readers[:2], mode, ids, merged(parts).shape[1]), merged(parts))
+        # automatic: a sample decides
+        abi.check(abi.lib.memb_b200_set_option(b"union_dedup", 1))
+        words = queries_for(syns[0], rng, 150_000)
+        before = abi.lib.memb_b200_launch_count()
+        check_words(words, 2)
+        with_distinct_path = abi.lib.memb_b200_launch_count() - before
+        abi.check(abi.lib.memb_b200_set_option(b"union_dedup", 0))
+        before = abi.lib.memb_b200_launch_count()
+        check_words(words, 2)
+        if mode_name == "average":  # (claim x 2, follow, copy-out on top; concatenate: the copy-out costs more than it saves)
+            assert with_distinct_path > abi.lib.memb_b200_launch_count() - before
+        for flavour in (2, 0):  # forced, with the element walk as the copy-out; off
+            abi.check(abi.lib.memb_b200_set_option(b"union_dedup", flavour))
+            abi.check(abi.lib.memb_b200_set_option(b"union_dedup_copy", 0))
+            abi.check(abi.lib.memb_b200_set_option(b"union_dedup_keys", 0))  # generic claim for two readers too
+            check_words(words[:5000], 2)
+    finally:
+        abi.lib.memb_b200_set_option(b"union_dedup", 1)
+        abi.lib.memb_b200_set_option(b"union_dedup_copy", 1)
+        abi.lib.memb_b200_set_option(b"union_dedup_keys", 1)
+        for r in readers:
+            r.close()
