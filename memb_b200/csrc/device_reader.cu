@@ -34,8 +34,8 @@ std::atomic<int64_t> g_optPassRows{0};
 std::atomic<int64_t> g_optSymAverage{1};
 std::atomic<int64_t> g_optPairTable{3};     // average through symbol words: 0 two gathers, 1 pair table (small codebooks), 2 + predicate-free middle-chunk flush, 3 + one table copy per bank
 std::atomic<int64_t> g_optUniformRows{1};
-std::atomic<int64_t> g_optDedupCopy{1};     // copy-out of the distinct path: 1 copy_rows_kernel, 0 full_gather_kernel (the element walk)
 std::atomic<int64_t> g_optDedupKeys{1};     // distinct path, one or two readers: 1 the tuple is the slot's 64-bit key, 0 the generic claim (slots hold query indices)
+std::atomic<int64_t> g_optDedupKeep{1};     // copy-out of the distinct path: loads carry an L2 evict_last hint
 std::atomic<int64_t> g_optDedup{1};         // union lookups of batches that repeat their words: 0 decode every query, 1 decode distinct id tuples once when a sample says the batch repeats (default), 2 always take the distinct path (tests)
 std::atomic<int64_t> g_optTrainedRows{0};   // trained_rows_kernel: 0 never (default: measured slower than the ring kernel), 1 unions of trained readers in ONE launch, 2 single lookups too
 std::atomic<int64_t> g_optRowsWarps{0};     // cap on resident warps of trained_rows_kernel (0 = as many as fit)
@@ -1368,12 +1368,12 @@ bool tryLaunchUnionDistinct(memb_b200_reader* const* readers, uint32_t R, memb_b
         CUDA_CHECK(cudaMemsetAsync(dCount, 0, 4, stream));
         CUDA_CHECK(cudaMemsetAsync(slots, 0xff, uint64_t(slotsUsed) * (packed ? 8 : 4), stream));
         if (packed) {
-            K::dedup_claim64_kernel<<<(queries + 255) / 256, 256, 0, stream>>>(
+            K::dedup_claim64_kernel<<<(queries + K::DEDUP_BLOCK - 1) / K::DEDUP_BLOCK, K::DEDUP_BLOCK, 0, stream>>>(
                 ids, idStride, R, queries, readers[0]->file->rows, R > 1 ? readers[1]->file->rows : 0u,
                 reinterpret_cast<unsigned long long*>(slots), slotsUsed - 1, reinterpret_cast<uint32_t*>(rep), compactOfSlot,
                 compact, distinctIds, n, dCount);
         } else {
-            K::dedup_claim_kernel<<<(queries + 255) / 256, 256, 0, stream>>>(ids, idStride, R, queries, slots, slotsUsed - 1,
+            K::dedup_claim_kernel<<<(queries + K::DEDUP_BLOCK - 1) / K::DEDUP_BLOCK, K::DEDUP_BLOCK, 0, stream>>>(ids, idStride, R, queries, slots, slotsUsed - 1,
                                                                               rep, compact, distinctIds, n, dCount);
         }
         ++g_launches;
@@ -1409,14 +1409,8 @@ bool tryLaunchUnionDistinct(memb_b200_reader* const* readers, uint32_t R, memb_b
     const bool vec = vec4Ok(static_cast<uint32_t>(unionDim), o);
     const uint64_t elems = n * (vec ? unionDim / 4 : unionDim);
     const unsigned grid = static_cast<unsigned>(std::min<uint64_t>((elems + 255) / 256, uint64_t(r0.numSMs) * 32));
-    if (vec && g_optDedupCopy.load()) {
-        const uint64_t groups = (n + K::COPY_ROWS - 1) / K::COPY_ROWS;  // one warp per group, 8 warps per block
-        const unsigned blocks = static_cast<unsigned>(std::min<uint64_t>((groups + 7) / 8, uint64_t(r0.numSMs) * 8));
-        auto go = [&](auto kernel) {
-            kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(release.rows), compact, n,
-                                               static_cast<uint32_t>(unionDim / 4), reinterpret_cast<float4*>(dOut));
-        };
-        g_optDedupCopy.load() == 2 ? go(K::copy_rows_kernel<true>) : go(K::copy_rows_kernel<false>);
+    if (vec && g_optDedupKeep.load()) {
+        K::full_gather_kernel<true, K::EPI_WRITE, false, true><<<grid, 256, 0, stream>>>(rows, compact, 0, n, o);
     } else if (vec) {
         K::full_gather_kernel<true, K::EPI_WRITE><<<grid, 256, 0, stream>>>(rows, compact, 0, n, o);
     } else {
@@ -1501,10 +1495,10 @@ memb_b200_status memb_b200_set_option(const char* name, int64_t value)
             g_optSymAverage = value;
         } else if (key == "union_dedup" && value >= 0 && value <= 2) {
             g_optDedup = value;
+        } else if (key == "union_dedup_keep" && (value == 0 || value == 1)) {
+            g_optDedupKeep = value;
         } else if (key == "union_dedup_keys" && (value == 0 || value == 1)) {
             g_optDedupKeys = value;
-        } else if (key == "union_dedup_copy" && value >= 0 && value <= 2) {
-            g_optDedupCopy = value;
         } else if (key == "union_pair_table" && value >= 0 && value <= 3) {
             g_optPairTable = value;
         } else if (key == "uniform_rows_kernel" && value >= 0 && value <= 2) {

@@ -1992,11 +1992,17 @@ struct FullState {
     float4 v;  // VEC4: four values; else .x
 };
 
-template <bool VEC4, int EPI, bool SIDE = false>
+// KEEP: the loads ask L2 to keep what they touch (evict_last) -- the copy-out of the distinct-tuples path, whose
+// source is far larger than L2 but whose frequent rows carry most of the reads while the output streams through.
+template <bool VEC4, int EPI, bool SIDE = false, bool KEEP = false>
 __global__ void full_gather_kernel(const FullParams p, const int32_t* __restrict__ ids, uint32_t rowBegin,
                                    uint64_t n, const OutputSpec o)
 {
     const uint32_t perRow = VEC4 ? p.dim / 4 : p.dim;
+    uint64_t keep = 0;
+    if (KEEP) {
+        asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep));
+    }
     forEachElement<FLAT_BATCH, FullState>(
         n, perRow,
         [&](uint64_t i, uint32_t c) {
@@ -2010,7 +2016,11 @@ __global__ void full_gather_kernel(const FullParams p, const int32_t* __restrict
             st.v = make_float4(0.f, 0.f, 0.f, 0.f);
             if (present) {
                 const float* src = p.values + static_cast<uint64_t>(row) * p.dim;
-                if (VEC4) {
+                if (VEC4 && KEEP) {
+                    asm volatile("ld.global.nc.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+                                 : "=f"(st.v.x), "=f"(st.v.y), "=f"(st.v.z), "=f"(st.v.w)
+                                 : "l"(reinterpret_cast<const float4*>(src) + c), "l"(keep));
+                } else if (VEC4) {
                     st.v = __ldg(reinterpret_cast<const float4*>(src) + c);
                 } else {
                     st.v.x = __ldg(src + c);
@@ -2051,6 +2061,53 @@ __global__ void full_gather_kernel(const FullParams p, const int32_t* __restrict
 // claimed it, -1 free).  rep[i] = the query whose tuple equals query i's and owns the slot; an owner also takes
 // the next compact index (warp-aggregated counter) and leaves its tuple in distinctIds.  A plain load in front of
 // the CAS keeps the 260 k copies of the most frequent word from queueing on one atomic.
+// A slot changes once (free -> claimed), so a claimed value seen through L1 is final and a stale "free" only costs
+// the CAS that tells the truth.  Through L1 on purpose: the slot of the batch's most frequent word is read by
+// 260 k queries, and uncached (volatile) loads of ONE sector queue on its L2 slice.
+__device__ __forceinline__ int32_t ldCachedI32(const int32_t* p)
+{
+    int32_t v;
+    asm volatile("ld.global.ca.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long ldCachedU64(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.global.ca.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+// Compact index of an owner: ONE atomicAdd on the batch's counter per BLOCK (a warp-aggregated atomic per warp was
+// 125 k atomics on one address for 4 M Zipf words -- 0.19 of the claim kernel's 0.21 ms, ncu launch list r02).
+// Every thread of the block calls it (two __syncthreads); returns the index for owners, junk otherwise.
+constexpr uint32_t DEDUP_BLOCK = 512;
+__device__ __forceinline__ uint32_t claimCompactIndex(bool owner, uint32_t* count)
+{
+    __shared__ uint32_t warpBase[DEDUP_BLOCK / WARP];
+    __shared__ uint32_t blockBase;
+    const uint32_t lane = threadIdx.x % WARP, warp = threadIdx.x / WARP;
+    const uint32_t owners = __ballot_sync(0xffffffffu, owner);
+    if (lane == 0) {
+        warpBase[warp] = __popc(owners);
+    }
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t mine = lane < blockDim.x / WARP ? warpBase[lane] : 0u;
+        uint32_t incl = mine;
+#pragma unroll
+        for (uint32_t d = 1; d < WARP; d *= 2) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
+            incl += lane >= d ? up : 0u;
+        }
+        if (lane < blockDim.x / WARP) {
+            warpBase[lane] = incl - mine;
+        }
+        if (lane == WARP - 1 && incl) {
+            blockBase = atomicAdd(count, incl);
+        }
+    }
+    __syncthreads();
+    return blockBase + warpBase[warp] + __popc(owners & ((1u << lane) - 1u));
+}
 __device__ __forceinline__ uint64_t tupleHash(const int32_t* __restrict__ ids, uint64_t idStride, uint32_t R, uint64_t i)
 {
     uint64_t h = 0x9e3779b97f4a7c15ull;
@@ -2065,13 +2122,12 @@ __global__ void dedup_claim_kernel(const int32_t* __restrict__ ids, uint64_t idS
                                    uint64_t distinctStride, uint32_t* count)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t lane = threadIdx.x % WARP;
     bool owner = false;
     if (i < n) {
         uint32_t slot = static_cast<uint32_t>(tupleHash(ids, idStride, R, i)) & slotMask;
         int32_t mine = static_cast<int32_t>(i);
         for (;;) {
-            int32_t cur = *reinterpret_cast<volatile int32_t*>(slots + slot);
+            int32_t cur = ldCachedI32(slots + slot);
             if (cur < 0) {
                 cur = atomicCAS(slots + slot, -1, static_cast<int32_t>(i));
                 if (cur < 0) {
@@ -2091,20 +2147,11 @@ __global__ void dedup_claim_kernel(const int32_t* __restrict__ ids, uint64_t idS
         }
         rep[i] = mine;
     }
-    const uint32_t owners = __ballot_sync(0xffffffffu, owner);
-    if (owners) {  // (warp-uniform)
-        const uint32_t leader = __ffs(owners) - 1;
-        uint32_t base = 0;
-        if (lane == leader) {
-            base = atomicAdd(count, __popc(owners));
-        }
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (owner) {
-            const uint32_t c = base + __popc(owners & ((1u << lane) - 1u));
-            compact[i] = static_cast<int32_t>(c);
-            for (uint32_t k = 0; k < R; ++k) {
-                distinctIds[k * distinctStride + c] = __ldg(ids + k * idStride + i);
-            }
+    const uint32_t c = claimCompactIndex(owner, count);
+    if (owner) {
+        compact[i] = static_cast<int32_t>(c);
+        for (uint32_t k = 0; k < R; ++k) {
+            distinctIds[k * distinctStride + c] = __ldg(ids + k * idStride + i);
         }
     }
 }
@@ -2121,7 +2168,6 @@ __global__ void dedup_claim64_kernel(const int32_t* __restrict__ ids, uint64_t i
 {
     constexpr unsigned long long EMPTY = ~0ull;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t lane = threadIdx.x % WARP;
     bool owner = false;
     uint32_t slot = 0;
     int32_t id0 = -1, id1 = -1;
@@ -2136,7 +2182,7 @@ __global__ void dedup_claim64_kernel(const int32_t* __restrict__ ids, uint64_t i
                                        static_cast<uint32_t>(id0 + 1);
         slot = static_cast<uint32_t>(mix64(key)) & slotMask;
         for (;;) {
-            unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(slots + slot);
+            unsigned long long cur = ldCachedU64(slots + slot);
             if (cur == EMPTY) {
                 cur = atomicCAS(slots + slot, EMPTY, key);
                 if (cur == EMPTY) {
@@ -2150,17 +2196,7 @@ __global__ void dedup_claim64_kernel(const int32_t* __restrict__ ids, uint64_t i
             slot = (slot + 1) & slotMask;
         }
     }
-    const uint32_t owners = __ballot_sync(0xffffffffu, owner);
-    uint32_t c = 0;
-    if (owners) {  // (warp-uniform)
-        const uint32_t leader = __ffs(owners) - 1;
-        uint32_t base = 0;
-        if (lane == leader) {
-            base = atomicAdd(count, __popc(owners));
-        }
-        base = __shfl_sync(0xffffffffu, base, leader);
-        c = base + __popc(owners & ((1u << lane) - 1u));
-    }
+    const uint32_t c = claimCompactIndex(owner, count);
     if (i < n) {
         slotOf[i] = slot | (owner ? 0x80000000u : 0u);
         if (owner) {
@@ -2192,69 +2228,6 @@ __global__ void dedup_follow_kernel(const int32_t* __restrict__ rep, int32_t* co
         const int32_t r = rep[i];
         if (r != static_cast<int32_t>(i)) {
             compact[i] = compact[r];
-        }
-    }
-}
-
-// The copy-out of the distinct-tuples path: out[i] = rows[index[i]], rows of `units` x 16 B.  A warp moves COPY_ROWS
-// consecutive output rows at a time (all loads in flight before the first store; the stores of a warp are one
-// contiguous run).  The temporary is far larger than L2 but its frequent rows carry most of the reads (Zipf):
-// the loads ask L2 to keep what they touch (evict_last) while the output streams through (evict-first stores) --
-// ncu r02 of the element walk it replaces: L2 hit rate 48 %, DRAM read 2.0 GB beside 4.7 GB written.
-constexpr int COPY_ROWS = 4;
-template <bool KEEP>
-__global__ void __launch_bounds__(256) copy_rows_kernel(const float4* __restrict__ rows, const int32_t* __restrict__ index,
-                                                        uint64_t n, uint32_t units, float4* __restrict__ out)
-{
-    const uint32_t lane = threadIdx.x % WARP;
-    const uint64_t warp = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) / WARP;
-    const uint64_t warps = static_cast<uint64_t>(gridDim.x) * (blockDim.x / WARP);
-    uint64_t keep;
-    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep));
-    constexpr int MAX_STEPS = 4;  // rows of up to 4 x 32 x 16 B = 2 KiB take the unrolled path
-    const uint32_t steps = (units + WARP - 1) / WARP;
-    for (uint64_t row0 = warp * COPY_ROWS; row0 < n; row0 += warps * COPY_ROWS) {
-        const uint32_t here = static_cast<uint32_t>(min(static_cast<uint64_t>(COPY_ROWS), n - row0));
-        if (steps <= MAX_STEPS) {
-            float4 v[COPY_ROWS][MAX_STEPS];
-            uint64_t src[COPY_ROWS];
-#pragma unroll
-            for (int r = 0; r < COPY_ROWS; ++r) {
-                src[r] = r < here ? static_cast<uint64_t>(__ldg(index + row0 + r)) * units : 0;
-            }
-#pragma unroll
-            for (int r = 0; r < COPY_ROWS; ++r) {
-#pragma unroll
-                for (int k = 0; k < MAX_STEPS; ++k) {
-                    const uint32_t u = lane + k * WARP;
-                    if (r < here && u < units) {
-                        if (KEEP) {
-                            asm volatile("ld.global.nc.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
-                                         : "=f"(v[r][k].x), "=f"(v[r][k].y), "=f"(v[r][k].z), "=f"(v[r][k].w)
-                                         : "l"(rows + src[r] + u), "l"(keep));
-                        } else {
-                            v[r][k] = __ldg(rows + src[r] + u);
-                        }
-                    }
-                }
-            }
-#pragma unroll
-            for (int r = 0; r < COPY_ROWS; ++r) {
-#pragma unroll
-                for (int k = 0; k < MAX_STEPS; ++k) {
-                    const uint32_t u = lane + k * WARP;
-                    if (r < here && u < units) {
-                        __stcs(out + (row0 + r) * units + u, v[r][k]);
-                    }
-                }
-            }
-        } else {
-            for (uint32_t r = 0; r < here; ++r) {
-                const uint64_t from = static_cast<uint64_t>(__ldg(index + row0 + r)) * units;
-                for (uint32_t u = lane; u < units; u += WARP) {
-                    __stcs(out + (row0 + r) * units + u, __ldg(rows + from + u));
-                }
-            }
         }
     }
 }

@@ -809,14 +809,12 @@ def test_union_distinct_tuples_path(abi, oracle, synthetic, mode_name):
         check_words(words, 2)
         if mode_name == "average":  # (claim x 2, follow, copy-out on top; concatenate: the copy-out costs more than it saves)
             assert with_distinct_path > abi.lib.memb_b200_launch_count() - before
-        for flavour in (2, 0):  # forced, with the element walk as the copy-out; off
+        for flavour in (2, 0):  # forced; off
             abi.check(abi.lib.memb_b200_set_option(b"union_dedup", flavour))
-            abi.check(abi.lib.memb_b200_set_option(b"union_dedup_copy", 0))
             abi.check(abi.lib.memb_b200_set_option(b"union_dedup_keys", 0))  # generic claim for two readers too
             check_words(words[:5000], 2)
     finally:
         abi.lib.memb_b200_set_option(b"union_dedup", 1)
-        abi.lib.memb_b200_set_option(b"union_dedup_copy", 1)
         abi.lib.memb_b200_set_option(b"union_dedup_keys", 1)
         for r in readers:
             r.close()
