@@ -193,7 +193,15 @@ void memb_b200_host_free(void* ptr);
 uint64_t memb_b200_launch_count(void);
 /* Knobs for experiments and tests: "trained_lut_replicas" = 0 auto | 1 | 32,
  * "trained_warps" = 0 auto | 1..10, "trained_generic" = 0|1 (one-thread-per-row decode),
+ * "trained_tma" = 0 | 1 (default: bulk-async staging for aligned range decodes and long records) | 2 everywhere,
+ * "trained_rows_kernel" = 0 (default) | 1 unions of trained readers in one launch | 2 single lookups too,
  * "union_symbol_average" = 0|1 (average of trained readers through symbol words),
+ * "union_pair_table" = 0 two gathers | 1 | 2 one table copy | 3 (default) one copy per shared-memory bank,
+ * "union_dedup" = 0 every query of a union lookup is decoded | 1 (default) batches of >= 131 072 queries that repeat
+ *   their id tuples (Zipf-distributed words) have the DISTINCT tuples decoded once and the rows copied out when a cost
+ *   model says that is cheaper -- same bytes; the decision takes two 4-byte device -> host round trips on the call's
+ *   stream, so it is skipped under stream capture | 2 always (tests),
+ * "union_dedup_keys", "union_dedup_keep" = 0|1 (its claim-kernel flavour, the L2 hint of its copy-out),
  * "uniform_rows_kernel" = 0 element walk | 1 auto (row-group kernel unless levels is a power of two) | 2 always,
  * "host_pass_rows" = rows staged per pass for host outputs (0 = 4 GiB of fp32).
  * Applies to readers opened / calls made afterwards. */
