@@ -746,7 +746,7 @@ void launchTrainedKernel(const memb_b200_reader& r, const int32_t* ids, uint32_t
     const K::TrainedLayout lay = K::trainedLayout(
         r.smemBase, K::trainedLutBytes(p.lutBits, p.lutReplicas),
         K::trainedWarpBytes(p.rowWords, TMA ? K::trainedLandingBytes(p.recUnits) : 0u), r.trainedWarps,
-        SYM == 2 ? o.pairEntries * o.pairReplicas : p.lut2Entries);
+        SYM >= 2 ? o.pairEntries * o.pairReplicas : p.lut2Entries);
     const size_t smemBytes = lay.end - r.smemBase;
     const uint64_t tiles = (n + 31) / 32;
     const unsigned grid = static_cast<unsigned>(
@@ -978,7 +978,10 @@ void launchTrainedVec(const memb_b200_reader& r, const int32_t* ids, uint32_t ro
     const bool rmw = epi != K::EPI_WRITE;
     if (o.sym) {
         // average of trained readers through symbol words (OutputSpec::sym)
-        if (rmw) {
+        if (rmw && o.pairEntries) {
+            small ? launchTrainedKernel<G, true, false, true, true, false, 3>(r, ids, rowBegin, n, o, epi, stream)
+                  : launchTrainedKernel<G, true, false, false, true, false, 3>(r, ids, rowBegin, n, o, epi, stream);
+        } else if (rmw) {
             small ? launchTrainedKernel<G, true, false, true, true, false, 2>(r, ids, rowBegin, n, o, epi, stream)
                   : launchTrainedKernel<G, true, false, false, true, false, 2>(r, ids, rowBegin, n, o, epi, stream);
         } else {

@@ -934,6 +934,7 @@ __device__ __forceinline__ uint32_t shflFrom(uint32_t v, uint32_t srcLane)
 // RMW: the launch carries an average epilogue (ACCUMULATE / FINALIZE): the fast flush
 // reads the running sum, adds, divides for the last reader, and stores.
 // SIDE: the launch redirects first / last units to side buffers (OutputSpec::sideHead).
+// SYM: 3 = 2 with the merged values taken from the pair table (OutputSpec::pairEntries != 0);
 // SYM: 1 = the launch stores symbol words instead of fp32 rows, 2 = the running sum it adds to
 // is gathered from another reader's symbol words (OutputSpec::sym).
 // TMA: the warp's 32 records reach shared memory through cp.async.bulk (one 1-D bulk copy per
@@ -953,6 +954,11 @@ __global__ void __maxnreg__(TRAINED_MAX_REGS)
 trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, uint32_t rowBegin, uint64_t n,
                       const OutputSpec o, const int epi, uint32_t* __restrict__ tileCounter)
 {
+    // SYM == 3 is SYM == 2 with the pair table as a compile-time fact: the two-gather flush, its adds and the divide
+    // sequences are not in the code at all (ncu r02 of the 82 KB SYM == 2 kernel, both flavours compiled in: stall
+    // no_instruction 1.16 per issue, 18 % of its samples, in the rarely executed first / last chunk flush)
+    constexpr int SYMK = SYM == 3 ? 2 : SYM;
+    constexpr bool PAIRS = SYM == 3;
     extern __shared__ __align__(128) unsigned char smem[];
     const uint32_t lane = threadIdx.x % WARP;
     const uint32_t warp = threadIdx.x / WARP;
@@ -961,8 +967,8 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     const uint32_t lutBytes = trainedLutBytes(p.lutBits, p.lutReplicas);
     const uint32_t base = smemAddr(smem);
     const uint32_t perWarp = trainedWarpBytes(p.rowWords, TMA ? trainedLandingBytes(p.recUnits) : 0u);
-    // (the region behind the codebooks holds the second-level table, or -- SYM == 2, never with long codes -- the pair table)
-    const TrainedLayout lay = trainedLayout(base, lutBytes, perWarp, warpsPerCta, SYM == 2 ? o.pairEntries * o.pairReplicas : p.lut2Entries);
+    // (the region behind the codebooks holds the second-level table, or -- SYMK == 2, never with long codes -- the pair table)
+    const TrainedLayout lay = trainedLayout(base, lutBytes, perWarp, warpsPerCta, SYMK == 2 ? o.pairEntries * o.pairReplicas : p.lut2Entries);
     {
         uint32_t dynBytes;
         asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dynBytes));
@@ -1001,7 +1007,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                 }
             }
         }
-        if (SYM == 2) {
+        if (PAIRS) {
             float* pairS = reinterpret_cast<float*>(smem + (lay.lut2 - base));
             for (uint32_t i = threadIdx.x; i < o.pairEntries; i += blockDim.x) {
                 const uint32_t s0 = i / o.pairStride, s1 = i % o.pairStride;
@@ -1027,7 +1033,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         }
         for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) {
             cbS[i] = i < p.codebookSize ? p.codebook[i] : 0.f;
-            if (SYM == 2) {
+            if (SYMK == 2) {
                 cbS[256 + i] = i < o.symCodebookSize ? o.symCodebook[i] : 0.f;
             }
         }
@@ -1050,7 +1056,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
     d.padL = p.padBits + p.lutBits;
     const uint32_t tileLane = tileRowBase(tile, lane);
     const uint64_t boundaryPolicy = boundaryStorePolicy();
-    const uint32_t pairBase = lay.lut2 + (SYM == 2 && o.pairReplicas != 1 ? lane * 4u : 0u);  // lane l reads bank l
+    const uint32_t pairBase = lay.lut2 + (SYMK == 2 && o.pairReplicas != 1 ? lane * 4u : 0u);  // lane l reads bank l
     // The flush reads ring slots it then does not store (units before the row in the
     // first chunk, units past it in the last).  With SMALLCB a symbol byte IS a shared
     // address offset, so those slots must never hold anything but multiples of 4.
@@ -1280,9 +1286,9 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         const uint32_t aStep = static_cast<uint32_t>(rowBytes >> 4) * TRAINED_FLUSH_ROWS;  // FLUSH_ROWS rows, in 16 B units
         const uint32_t tileRows = tileRowBase(tile, fr);  // rows 4*it + fr: + it * TRAINED_TILE_GROUP_BYTES
         // SYM: symbol words of row 4*it + fr of this tile start at symRow0 + it * symStep
-        uint32_t* const symRow0 = SYM ? o.sym + (row0 + fr) * o.symWords : nullptr;
+        uint32_t* const symRow0 = SYMK ? o.sym + (row0 + fr) * o.symWords : nullptr;
         const uint64_t symStep = static_cast<uint64_t>(TRAINED_FLUSH_ROWS) * o.symWords;
-        const uint32_t cb0 = cb + 1024;  // the other reader's codebook (SYM == 2)
+        const uint32_t cb0 = cb + 1024;  // the other reader's codebook (SYMK == 2)
         // A lane without a row (missing word) decodes row 0 like the others but writes the
         // symbol of the codebook's +0.0 slot to the tile, so the straight-line flush needs no
         // per-row predicate: only a ragged last tile (or a codebook with no free slot) takes
@@ -1297,7 +1303,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         for (uint32_t c0 = 0; c0 < dim; c0 += TRAINED_CHUNK) {
             const uint32_t nsym = min(TRAINED_CHUNK, dim - c0);
             const uint32_t word0 = (c0 / 4) & (TRAINED_RING_UNITS - 1);  // ring position of this chunk's first word
-            // SYM == 2: the symbol words this chunk's flush adds to are LOADED here, before the decode, and
+            // SYMK == 2: the symbol words this chunk's flush adds to are LOADED here, before the decode, and
             // consumed after it (eight registers per lane; fp32 running sums would be 32: L2 prefetch only).
             // Measured r02 on the two-reader average, 1 M Zipf words (stable once the stream-ordered pool kept
             // its memory): 0.777 ms two-gather flush -> 0.752 with the pair table -> 0.723 with the
@@ -1314,7 +1320,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                 for (uint32_t it = 0; it < TRAINED_CHUNK_UNITS; ++it) {
                     const int a = int((aBase + it * aStep) & 7u);
                     const int j = ub - a + int(fq);
-                    if (SYM == 2) {
+                    if (SYMK == 2) {
                         // (exactly the predicate of the flush's first pass)
                         symAhead[it] = ldU32If(j >= 0 && j < (lastChunk ? ua : ua - a), symRow0 + it * symStep + j);
                     } else {
@@ -1366,7 +1372,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                 const bool last = c0 + TRAINED_CHUNK >= dim;
                 const int unitsBefore = int(c0 / 4);
                 const int unitsAfter = int((c0 + nsym) / 4);
-                if (SYM == 2 && fastFlush && RMW && !last && c0 != 0 && o.pairEntries && o.straightPairs) {
+                if (PAIRS && fastFlush && RMW && !last && c0 != 0 && o.straightPairs) {
                     // pair-table average, middle chunk: every unit of the lagged window exists -- no predicates,
                     // no pass loop, address math on two elements per instruction (gatherPairsWide)
                     const uint32_t m0 = (o.pairStride * o.pairReplicas) << o.symFieldShift;
@@ -1394,7 +1400,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int a = int((aBase + it * aStep) & 7u);
                             const int j = unitsBefore - a + int(fq) + shift;
                             const int end = last ? end0 : unitsAfter - a;
-                            if (SYM == 2) {
+                            if (SYMK == 2) {
                                 old[it].x = __uint_as_float(pass == 0 ? symAhead[it]
                                                                       : ldU32If(j >= 0 && j < end, symRow0 + it * symStep + j));
                             } else {
@@ -1408,12 +1414,12 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int end = last ? end0 : unitsAfter - a;
                             const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
                             float4 v;
-                            if (SYM == 2 && o.pairEntries) {
+                            if (PAIRS) {
                                 v = gatherPairs(pairBase, __float_as_uint(old[it].x), s4,
                                                 (o.pairStride * o.pairReplicas) << o.symFieldShift,
                                                 o.pairReplicas * (SMALLCB ? 1u : 4u));
                             } else {
-                                const float4 sum = SYM == 2 ? gatherCentroidsShift(cb0, __float_as_uint(old[it].x), o.symFieldShift)
+                                const float4 sum = SYMK == 2 ? gatherCentroidsShift(cb0, __float_as_uint(old[it].x), o.symFieldShift)
                                                             : old[it];
                                 v = applyEpilogue4(gatherCentroids<SMALLCB>(cb, s4), sum, epi, o.divisor);
                             }
@@ -1438,7 +1444,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int a = int((aBase + it * aStep) & 7u);
                             const int j = unitsBefore - a + int(fq);
                             const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
-                            if (SYM == 1) {
+                            if (SYMK == 1) {
                                 symRow0[it * symStep + j] = s4;
                                 continue;
                             }
@@ -1452,7 +1458,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int j = unitsBefore - a + int(fq);
                             const int end = last ? unitsAfter : unitsAfter - a;
                             const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j));
-                            if (SYM == 1) {
+                            if (SYMK == 1) {
                                 stU32If(j >= 0 && j < end, symRow0 + it * symStep + j, s4);
                                 continue;
                             }
@@ -1473,7 +1479,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                                 const int a = int((aBase + it * aStep) & 7u);
                                 const int j2 = unitsBefore - a + int(fq) + int(TRAINED_CHUNK_UNITS);
                                 const uint32_t s4 = ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j2));
-                                if (SYM == 1) {
+                                if (SYMK == 1) {
                                     stU32If(j2 < unitsAfter, symRow0 + it * symStep + j2, s4);
                                     continue;
                                 }
@@ -1500,7 +1506,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                             const int end = last ? unitsAfter : unitsAfter - a;
                             const bool rowPresent = (presentMask >> r) & 1u;
                             for (int j = begin + int(fq); j < end; j += int(TRAINED_CHUNK_UNITS)) {
-                                if (SYM == 1) {
+                                if (SYMK == 1) {
                                     o.sym[(row0 + r) * o.symWords + j] =
                                         rowPresent ? ldsU32(tileRows + it * TRAINED_TILE_GROUP_BYTES + tileWordOffset(j)) : p.zeroWord;
                                     continue;
@@ -1515,7 +1521,7 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
                                     dst = redirectUnit(o, dst, row0 + r, static_cast<uint32_t>(j), dim / 4 - 1);
                                 }
                                 if (epi != EPI_WRITE) {
-                                    const float4 old = SYM == 2 ? gatherCentroidsShift(cb0, o.sym[(row0 + r) * o.symWords + j],
+                                    const float4 old = SYMK == 2 ? gatherCentroidsShift(cb0, o.sym[(row0 + r) * o.symWords + j],
                                                                                        o.symFieldShift)
                                                                 : *dst;
                                     v.x = applyEpilogue(v.x, old.x, epi, o.divisor);

@@ -32,4 +32,5 @@ for setting in a.settings:
     print(json.dumps({"setting": setting, "words": a.words, "parity": r["parity"],
                       **{m: {"ms_decode": round(r[m]["ms_decode"], 4), "ms_resolve_and_decode": round(r[m]["ms_resolve_and_decode"], 4),
                              "frac_decode": round(r[m]["roofline_frac_decode_per_gpu"], 3),
+                             "every_query_ms_decode": round(r[m]["every_query_decoded"]["ms_decode"], 4),
                              "launches": r[m]["launches_per_call"]} for m in ("average", "concatenate")}}), flush=True)
