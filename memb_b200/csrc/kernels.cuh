@@ -1289,6 +1289,16 @@ trained_decode_kernel(const TrainedParams p, const int32_t* __restrict__ ids, ui
         uint32_t* const symRow0 = SYMK ? o.sym + (row0 + fr) * o.symWords : nullptr;
         const uint64_t symStep = static_cast<uint64_t>(TRAINED_FLUSH_ROWS) * o.symWords;
         const uint32_t cb0 = cb + 1024;  // the other reader's codebook (SYMK == 2)
+        if (SYMK == 2 && rowsHere == WARP) {
+            // The tile's symbol words (32 rows x symWords, one contiguous run) are pulled into L2 now: the register
+            // loads a chunk ahead of their use were still in flight when the flush wanted them (ncu r02: long
+            // scoreboard on the flush's first PRMT, 10 % of the launch's samples) -- from L2 they are not.
+            const char* const symTile = reinterpret_cast<const char*>(o.sym + row0 * o.symWords);
+            const uint32_t symBytes = WARP * o.symWords * 4u;
+            for (uint32_t b = lane * 128u; b < symBytes; b += WARP * 128u) {
+                prefetchL2If(true, symTile + b);
+            }
+        }
         // A lane without a row (missing word) decodes row 0 like the others but writes the
         // symbol of the codebook's +0.0 slot to the tile, so the straight-line flush needs no
         // per-row predicate: only a ragged last tile (or a codebook with no free slot) takes
