@@ -35,6 +35,7 @@ std::atomic<int64_t> g_optSymAverage{1};
 std::atomic<int64_t> g_optPairTable{3};     // average through symbol words: 0 two gathers, 1 pair table (small codebooks), 2 + predicate-free middle-chunk flush, 3 + one table copy per bank
 std::atomic<int64_t> g_optUniformRows{1};
 std::atomic<int64_t> g_optDedupKeys{1};     // distinct path, one or two readers: 1 the tuple is the slot's 64-bit key, 0 the generic claim (slots hold query indices)
+std::atomic<int64_t> g_optDedupSymbols{1};  // distinct path, average of two trained readers with small codebooks: the temporary holds symbol words, pair_gather_kernel merges on the way out
 std::atomic<int64_t> g_optDedupKeep{1};     // copy-out of the distinct path: loads carry an L2 evict_last hint
 std::atomic<int64_t> g_optDedup{1};         // union lookups of batches that repeat their words: 0 decode every query, 1 decode distinct id tuples once when a sample says the batch repeats (default), 2 always take the distinct path (tests)
 std::atomic<int64_t> g_optTrainedRows{0};   // trained_rows_kernel: 0 never (default: measured slower than the ring kernel), 1 unions of trained readers in ONE launch, 2 single lookups too
@@ -1404,6 +1405,40 @@ bool tryLaunchUnionDistinct(memb_b200_reader* const* readers, uint32_t R, memb_b
     }
     ++g_launches;
     CUDA_CHECK(cudaGetLastError());
+    // Average of two trained readers with small codebooks: the temporary holds the distinct tuples' SYMBOL words
+    // (two symbol-word launches) and pair_gather_kernel merges them on the way out -- half the bytes per output row
+    // to read back, no fp32 flush for the distinct tuples.
+    if (g_optDedupSymbols.load() && mode == MEMB_B200_AVERAGE && R == 2 && distinct > 0) {
+        const memb_b200_reader& ra = *readers[0];
+        const memb_b200_reader& rb = *readers[1];
+        K::OutputSpec probe{dOut, unionDim, 0, 1.0f};
+        auto tiled = [&](const memb_b200_reader& r) {
+            return r.file->storage == STORAGE_TRAINED && r.trainedWarps != 0 && !r.trainedEscape && r.trained.hasZeroSlot &&
+                   r.file->dim == unionDim && vec4Ok(r.file->dim, probe);
+        };
+        const uint32_t entries = (ra.trained.codebookSize + 1) * (rb.trained.codebookSize + 1);
+        if (tiled(ra) && tiled(rb) && entries * 128u <= 48u * 1024u && g_optSymAverage.load()) {
+            const uint32_t words = static_cast<uint32_t>(unionDim / 4);
+            const uint64_t symWordsPerReader = uint64_t(distinct) * words;
+            CUDA_CHECK(cudaMallocAsync(reinterpret_cast<void**>(&release.rows), 2 * symWordsPerReader * 4, stream));
+            uint32_t* sym = reinterpret_cast<uint32_t*>(release.rows);
+            for (uint32_t k = 0; k < 2; ++k) {
+                K::OutputSpec o{dOut, unionDim, 0, 1.0f};  // (a symbol-word launch writes nothing to `out`)
+                o.sym = sym + k * symWordsPerReader;
+                o.symWords = words;
+                launchDecode(*readers[k], distinctIds + k * n, 0, distinct, o, K::EPI_WRITE, stream);
+            }
+            const uint64_t groups = (n + 31) / 32;
+            const unsigned blocks = static_cast<unsigned>(std::min<uint64_t>(groups, uint64_t(r0.numSMs) * 6));
+            K::pair_gather_kernel<<<blocks, 256, entries * 128u, stream>>>(
+                sym, sym + symWordsPerReader, compact, n, words, ra.trained.codebook, ra.trained.codebookSize,
+                2u - ra.trained.symShift, rb.trained.codebook, rb.trained.codebookSize, 2u - rb.trained.symShift,
+                static_cast<float>(R), reinterpret_cast<float4*>(dOut));
+            ++g_launches;
+            CUDA_CHECK(cudaGetLastError());
+            return true;
+        }
+    }
     CUDA_CHECK(cudaMallocAsync(reinterpret_cast<void**>(&release.rows), uint64_t(distinct) * unionDim * 4, stream));
     launchUnion(readers, R, mode, distinctIds, n, 0, distinct, release.rows, unionDim, stream);
     // the copy-out: K3 over the temporary (compact index = row of the temporary; every index is in range)
@@ -1498,6 +1533,8 @@ memb_b200_status memb_b200_set_option(const char* name, int64_t value)
             g_optSymAverage = value;
         } else if (key == "union_dedup" && value >= 0 && value <= 2) {
             g_optDedup = value;
+        } else if (key == "union_dedup_symbols" && (value == 0 || value == 1)) {
+            g_optDedupSymbols = value;
         } else if (key == "union_dedup_keep" && (value == 0 || value == 1)) {
             g_optDedupKeep = value;
         } else if (key == "union_dedup_keys" && (value == 0 || value == 1)) {

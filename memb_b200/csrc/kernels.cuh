@@ -2248,5 +2248,52 @@ __global__ void dedup_follow_kernel(const int32_t* __restrict__ rep, int32_t* co
     }
 }
 
+// The copy-out of the distinct-tuples path for the average of two trained readers with small codebooks: the temporary
+// holds the distinct tuples' SYMBOL words of both readers (two SYM = 1 launches: dim bytes per row and reader instead
+// of 4 * dim of fp32), and this kernel turns them into rows on the way out -- out[i] = T[symA[index[i]]][symB[index[i]]]
+// with the per-bank pair table of the merged flush (same arithmetic: bit-identical).  Half the bytes to read per
+// output row, twice the rows of the temporary in L2, and the distinct tuples never go through the fp32 flush.
+struct PairGatherState {
+    float4* dst;
+    uint32_t a, b;
+};
+__global__ void __launch_bounds__(256) pair_gather_kernel(const uint32_t* __restrict__ symA, const uint32_t* __restrict__ symB,
+                                                          const int32_t* __restrict__ index, uint64_t n, uint32_t words,
+                                                          const float* __restrict__ codebook0, uint32_t size0, uint32_t fieldShift0,
+                                                          const float* __restrict__ codebook1, uint32_t size1, uint32_t fieldShift1,
+                                                          float divisor, float4* __restrict__ out)
+{
+    extern __shared__ __align__(128) unsigned char pairSmem[];
+    float* table = reinterpret_cast<float*>(pairSmem);
+    const uint32_t stride = size1 + 1;
+    const uint32_t entries = (size0 + 1) * stride;
+    for (uint32_t i = threadIdx.x; i < entries; i += blockDim.x) {
+        const uint32_t s0 = i / stride, s1 = i % stride;
+        const float c0 = s0 < size0 ? codebook0[s0] : 0.f;
+        const float c1 = s1 < size1 ? codebook1[s1] : 0.f;
+        const float t = applyEpilogue(c1, c0, EPI_FINALIZE, divisor);
+        float4* dst = reinterpret_cast<float4*>(table + i * WARP);
+#pragma unroll
+        for (uint32_t q = 0; q < WARP / 4; ++q) {
+            dst[q] = make_float4(t, t, t, t);
+        }
+    }
+    __syncthreads();
+    const uint32_t pairBase = smemAddr(table) + (threadIdx.x % WARP) * 4u;  // lane l reads bank l
+    // a field is symbol << (2 - fieldShift): byte offset of entry (s0, s1) = (s0 * stride + s1) * 128
+    const uint32_t m0 = (stride * WARP) << fieldShift0, m1 = WARP << fieldShift1;
+    forEachElement<FLAT_BATCH, PairGatherState>(
+        n, words,
+        [&](uint64_t i, uint32_t c) {
+            PairGatherState st;
+            const uint64_t row = static_cast<uint64_t>(__ldg(index + i)) * words + c;
+            st.a = __ldg(symA + row);
+            st.b = __ldg(symB + row);
+            st.dst = out + i * words + c;
+            return st;
+        },
+        [&](const PairGatherState& st) { __stcs(st.dst, gatherPairsWide(pairBase, st.a, st.b, m0, m1)); });
+}
+
 }  // namespace kernels
 }  // namespace memb_b200

@@ -794,6 +794,17 @@ def test_union_distinct_tuples_path(abi, oracle, synthetic, mode_name):
             check_words(sorted(set(queries_for(syns[1], rng, 500))), count)           # no repeats at all
             check_words(queries_for(syns[0], rng, 2), count)
         assert abi.lib.memb_b200_launch_count() > launches
+        # two SMALL codebooks (16 and 8 centroids): the temporary holds symbol words and pair_gather_kernel merges them
+        # on the way out (average only; union_dedup_symbols = 0: the fp32 temporary for the same batch)
+        small = synthetic("trained", 3, rows=600, dim=dim, seed=64)
+        pair_readers, pair_oracles = [readers[0], abi.open_checked(small.path)], [oracles[0], oracle.open(small.path)]
+        for symbols in (1, 0):
+            abi.check(abi.lib.memb_b200_set_option(b"union_dedup_symbols", symbols))
+            for words in ([w for i in rng.zipf(1.2, 2111) for w in [(syns[0].words + small.words + ["absent"])[i % 1501]]],
+                          [small.words[3]] * 40, queries_for(small, rng, 33)):
+                want = merged([o.batch_embedding(words) for o in pair_oracles])
+                assert bits_equal(helpers.union_lookup_words(abi, pair_readers, mode, words, want.shape[1]), want)
+        pair_readers[1].close()
         # id tuples that no word would produce (the ids entry point takes any): equal tuples share a row, others do not
         ids = np.stack([rng.integers(-2, 12, 4000), rng.integers(-1, 9, 4000)]).astype(np.int32)
         parts = [o.batch_ids(ids[k]) for k, o in enumerate(oracles[:2])]
@@ -816,5 +827,6 @@ def test_union_distinct_tuples_path(abi, oracle, synthetic, mode_name):
     finally:
         abi.lib.memb_b200_set_option(b"union_dedup", 1)
         abi.lib.memb_b200_set_option(b"union_dedup_keys", 1)
+        abi.lib.memb_b200_set_option(b"union_dedup_symbols", 1)
         for r in readers:
             r.close()
