@@ -201,7 +201,8 @@ uint64_t memb_b200_launch_count(void);
  *   their id tuples (Zipf-distributed words) have the DISTINCT tuples decoded once and the rows copied out when a cost
  *   model says that is cheaper -- same bytes; the decision takes two 4-byte device -> host round trips on the call's
  *   stream, so it is skipped under stream capture | 2 always (tests),
- * "union_dedup_keys", "union_dedup_keep" = 0|1 (its claim-kernel flavour, the L2 hint of its copy-out),
+ * "union_dedup_keys", "union_dedup_keep", "union_dedup_symbols" = 0|1 (its claim-kernel flavour, the L2 hint of its
+ *   copy-out, symbol words instead of fp32 rows as its temporary),
  * "uniform_rows_kernel" = 0 element walk | 1 auto (row-group kernel unless levels is a power of two) | 2 always,
  * "host_pass_rows" = rows staged per pass for host outputs (0 = 4 GiB of fp32).
  * Applies to readers opened / calls made afterwards. */
