@@ -195,6 +195,9 @@ uint64_t memb_b200_launch_count(void);
  * "trained_warps" = 0 auto | 1..10, "trained_generic" = 0|1 (one-thread-per-row decode),
  * "trained_tma" = 0 | 1 (default: bulk-async staging for aligned range decodes and long records) | 2 everywhere,
  * "trained_rows_kernel" = 0 (default) | 1 unions of trained readers in one launch | 2 single lookups too,
+ * "trained_rows_warps" = 0 auto | cap on that kernel's resident warps,
+ * "trained_fixed_records" = 0 | 1 (default: rows as fixed-stride records when the longest row is within 25 % of the
+ *   average), "trained_record_align" = 1 (default) | 2 | 4 (record stride a multiple of this many 16 B units),
  * "union_symbol_average" = 0|1 (average of trained readers through symbol words),
  * "union_pair_table" = 0 two gathers | 1 | 2 one table copy | 3 (default) one copy per shared-memory bank,
  * "union_dedup" = 0 every query of a union lookup is decoded | 1 (default) batches of >= 131 072 queries that repeat

@@ -383,3 +383,16 @@ def test_flatbufferbuilder_layout_is_read(abi, oracle, workdir):
         if soffset < 0 and 0 <= vt < len(data) - 4 and data[vt:vt + 4] == b"\x08\x00\x0c\x00":
             negatives += 1
     assert negatives >= len(words) - 1
+
+
+def test_every_option_is_documented_in_the_header():
+    """memb_b200_set_option's names (device_reader.cu) all appear in the comment of include/memb_b200.h."""
+    import re
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    source = open(os.path.join(root, "memb_b200", "csrc", "device_reader.cu")).read()
+    header = open(os.path.join(root, "include", "memb_b200.h")).read()
+    names = set(re.findall(r'key == "([a-z0-9_]+)"', source))
+    assert len(names) >= 10
+    undocumented = sorted(n for n in names if '"%s"' % n not in header)
+    assert not undocumented, undocumented
