@@ -1348,7 +1348,10 @@ bool tryLaunchUnionDistinct(memb_b200_reader* const* readers, uint32_t R, memb_b
     // one block: count | slots (x2 when 64-bit, + compactOfSlot) | rep or slotOf | compact | distinct ids (R x n)
     const uint64_t words = 64 + uint64_t(tableSlots) * (packed ? 3 : 1) + 2 * n + uint64_t(R) * n;
     int32_t* block = nullptr;
-    CUDA_CHECK(cudaMallocAsync(reinterpret_cast<void**>(&block), words * 4, stream));
+    if (cudaMallocAsync(reinterpret_cast<void**>(&block), words * 4, stream) != cudaSuccess) {
+        cudaGetLastError();  // no room for the tables: decode every query
+        return false;
+    }
     struct Release {
         int32_t* p;
         float* rows = nullptr;
@@ -1420,7 +1423,11 @@ bool tryLaunchUnionDistinct(memb_b200_reader* const* readers, uint32_t R, memb_b
         if (tiled(ra) && tiled(rb) && entries * 128u <= 48u * 1024u && g_optSymAverage.load()) {
             const uint32_t words = static_cast<uint32_t>(unionDim / 4);
             const uint64_t symWordsPerReader = uint64_t(distinct) * words;
-            CUDA_CHECK(cudaMallocAsync(reinterpret_cast<void**>(&release.rows), 2 * symWordsPerReader * 4, stream));
+            if (cudaMallocAsync(reinterpret_cast<void**>(&release.rows), 2 * symWordsPerReader * 4, stream) != cudaSuccess) {
+                cudaGetLastError();
+                release.rows = nullptr;
+                return false;
+            }
             uint32_t* sym = reinterpret_cast<uint32_t*>(release.rows);
             for (uint32_t k = 0; k < 2; ++k) {
                 K::OutputSpec o{dOut, unionDim, 0, 1.0f};  // (a symbol-word launch writes nothing to `out`)
@@ -1439,7 +1446,11 @@ bool tryLaunchUnionDistinct(memb_b200_reader* const* readers, uint32_t R, memb_b
             return true;
         }
     }
-    CUDA_CHECK(cudaMallocAsync(reinterpret_cast<void**>(&release.rows), uint64_t(distinct) * unionDim * 4, stream));
+    if (cudaMallocAsync(reinterpret_cast<void**>(&release.rows), uint64_t(distinct) * unionDim * 4, stream) != cudaSuccess) {
+        cudaGetLastError();  // no room for the temporary: decode every query
+        release.rows = nullptr;
+        return false;
+    }
     launchUnion(readers, R, mode, distinctIds, n, 0, distinct, release.rows, unionDim, stream);
     // the copy-out: K3 over the temporary (compact index = row of the temporary; every index is in range)
     K::FullParams rows{release.rows, distinct, static_cast<uint32_t>(unionDim)};
